@@ -1,0 +1,224 @@
+// UNet kernels that are not GEMM-shaped: weight packing / BN folding, the
+// Cin=1 first conv (K=9, CUDA cores, fp32), MC-dropout mask generation, the
+// bottleneck average pool, and a plain SIMT convolution used only by tests to
+// cross-check the tcgen05 path on the same packed operands.
+#pragma once
+
+#include "common.cuh"
+
+namespace b200al {
+
+// Conv2d weight [Cout][Cin][3][3] fp32 -> packed [plane][tap][Cout][Cin] bf16 (hi, lo).
+__global__ void pack_conv3x3_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wp, int cout, int cin) {
+  const int total = cout * cin * 9;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int tap = i % 9;
+    const int ci = (i / 9) % cin;
+    const int co = i / (9 * cin);
+    __nv_bfloat16 hi, lo;
+    split_bf16(w[i], hi, lo);
+    const size_t o = ((size_t)tap * cout + co) * cin + ci;
+    wp[o] = hi;
+    wp[(size_t)9 * cout * cin + o] = lo;
+  }
+}
+
+// ConvTranspose2d weight [Cin][Cout][2][2] -> packed [plane][quad*Cout + co][Cin], quad = dy*2+dx.
+__global__ void pack_convT_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wp, int cin, int cout) {
+  const int total = cin * cout * 4;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int quad = i % 4;
+    const int co = (i / 4) % cout;
+    const int ci = i / (4 * cout);
+    __nv_bfloat16 hi, lo;
+    split_bf16(w[i], hi, lo);
+    const size_t o = ((size_t)quad * cout + co) * cin + ci;
+    wp[o] = hi;
+    wp[(size_t)4 * cout * cin + o] = lo;
+  }
+}
+
+// BatchNorm (eval) folded to y = (acc + bias) * scale + shift (blocks.py:98;
+// Dropout2d sits between conv and BN, so the MC mask multiplies `scale`).
+__global__ void fold_bn_kernel(const float* gamma, const float* beta, const float* mean, const float* var, float eps,
+                               float* scale, float* shift, int c) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < c) {
+    const float s = gamma[i] / sqrtf(var[i] + eps);
+    scale[i] = s;
+    shift[i] = beta[i] - mean[i] * s;
+  }
+}
+
+__global__ void fill_kernel(float* p, float v, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
+// mask[s][ch] for s = b*T + t: 0 or 1/(1-p); keep iff hash24 >= thr.
+__global__ void mc_mask_kernel(float* __restrict__ mask, int n_samples, int T, int n_ch, uint64_t seed,
+                               long long base_pos, uint32_t thr, float keep_scale) {
+  const long long total = (long long)n_samples * n_ch;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int ch = (int)(i % n_ch);
+    const int s = (int)(i / n_ch);
+    const int b = s / T, t = s - b * T;
+    mask[i] = mc_hash24(seed, (uint64_t)(base_pos + b), (uint32_t)t, (uint32_t)ch) >= thr ? keep_scale : 0.f;
+  }
+}
+
+// First conv: 1 -> 32 channels, 3x3, pad 1, fp32 math on CUDA cores (K = 9).
+// One thread per output pixel, all 32 channels; sample s reads image s / T.
+template <typename ImgT>
+__global__ void __launch_bounds__(256)
+conv_first_kernel(const ImgT* __restrict__ img, int T, int H, int W, const float* __restrict__ w /*[32][9]*/,
+                  const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
+                  const float* __restrict__ mask, int mask_stride, float slope, __nv_bfloat16* __restrict__ out,
+                  int out_pitch, int hi_off, int lo_off, int write_lo) {
+  __shared__ float sw[32 * 9];
+  __shared__ float ses[32], seh[32];
+  const int s = blockIdx.z;
+  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
+  if (threadIdx.x < 32) {
+    float sc = scale[threadIdx.x];
+    if (mask) sc *= mask[(size_t)s * mask_stride + threadIdx.x];
+    ses[threadIdx.x] = sc;
+    seh[threadIdx.x] = bias[threadIdx.x] * sc + shift[threadIdx.x];
+  }
+  __syncthreads();
+  const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int y = blockIdx.y;
+  if (x >= W) return;
+  const ImgT* im = img + (size_t)(s / T) * H * W;
+  float v[9];
+#pragma unroll
+  for (int r = 0; r < 3; ++r)
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      const int yy = y + r - 1, xx = x + c - 1;
+      float t = 0.f;
+      if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
+        if (sizeof(ImgT) == 1) t = (float)im[(size_t)yy * W + xx] / 255.0f;  // torchvision to_tensor
+        else t = (float)im[(size_t)yy * W + xx];
+      }
+      v[r * 3 + c] = t;
+    }
+  __nv_bfloat16* dst = out + ((size_t)((size_t)s * H + y) * W + x) * out_pitch;
+  uint32_t hi[16], lo[16];
+#pragma unroll
+  for (int co = 0; co < 32; co += 2) {
+    float a0 = 0.f, a1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < 9; ++k) {
+      a0 = fmaf(v[k], sw[co * 9 + k], a0);
+      a1 = fmaf(v[k], sw[(co + 1) * 9 + k], a1);
+    }
+    a0 = leaky(a0 * ses[co] + seh[co], slope);
+    a1 = leaky(a1 * ses[co + 1] + seh[co + 1], slope);
+    __nv_bfloat16 h0, l0, h1, l1;
+    split_bf16(a0, h0, l0);
+    split_bf16(a1, h1, l1);
+    hi[co / 2] = pack_bf16x2(h0, h1);
+    lo[co / 2] = pack_bf16x2(l0, l1);
+  }
+  uint4* dh = reinterpret_cast<uint4*>(dst + hi_off);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+  if (write_lo) {
+    uint4* dl = reinterpret_cast<uint4*>(dst + lo_off);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+  }
+}
+
+// Bottleneck global average pool (unet.py:92): [S, HW, pitch] hi/lo -> [S, C] fp32.
+__global__ void avgpool_kernel(const __nv_bfloat16* __restrict__ act, int hw, int pitch, int hi_off, int lo_off,
+                               int use_lo, int c_total, float* __restrict__ emb) {
+  const int s = blockIdx.x;
+  for (int c = threadIdx.x; c < c_total; c += blockDim.x) {
+    const __nv_bfloat16* base = act + (size_t)s * hw * pitch + c;
+    float acc = 0.f;
+    for (int i = 0; i < hw; ++i) {
+      float v = __bfloat162float(base[(size_t)i * pitch + hi_off]);
+      if (use_lo) v += __bfloat162float(base[(size_t)i * pitch + lo_off]);
+      acc += v;
+    }
+    emb[(size_t)s * c_total + c] = acc / (float)hw;
+  }
+}
+
+// TEST-ONLY: direct convolution on CUDA cores over the same NHWC hi/lo
+// activations and packed weights the tcgen05 kernel consumes.  fp32 FMA.
+// One thread per (output pixel, cout).  mode 0: 3x3 conv (stride 1|2, pad 1);
+// mode 1: 2x2 stride-2 transposed conv.
+struct ConvSimtParams {
+  const __nv_bfloat16* in;
+  long long in_pitch;
+  int in_lo_off, in_H, in_W, cin;
+  const __nv_bfloat16* wp;  // packed as for the tcgen05 kernel
+  int cout, stride, mode, use_lo;
+  const float *scale, *bias, *shift, *mask;
+  int mask_stride;
+  float slope;
+  __nv_bfloat16* out;
+  long long out_pitch;
+  int out_hi_off, out_lo_off, out_H, out_W, write_lo;
+};
+
+__global__ void conv_simt_kernel(const ConvSimtParams p, int n_samples) {
+  const long long total = (long long)n_samples * p.out_H * p.out_W * p.cout;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int co = (int)(i % p.cout);
+    long long pix = i / p.cout;
+    const int ox = (int)(pix % p.out_W);
+    pix /= p.out_W;
+    const int oy = (int)(pix % p.out_H);
+    const int s = (int)(pix / p.out_H);
+    float acc = 0.f;
+    const int taps = p.mode == 0 ? 9 : 4;
+    const size_t plane = (size_t)taps * p.cout * p.cin;
+    if (p.mode == 0) {
+      for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) {
+          const int iy = oy * p.stride + r - 1, ix = ox * p.stride + c - 1;
+          if (iy < 0 || iy >= p.in_H || ix < 0 || ix >= p.in_W) continue;
+          const __nv_bfloat16* a = p.in + ((size_t)((size_t)s * p.in_H + iy) * p.in_W + ix) * p.in_pitch;
+          const __nv_bfloat16* w = p.wp + ((size_t)(r * 3 + c) * p.cout + co) * p.cin;
+          for (int ci = 0; ci < p.cin; ++ci) {
+            float av = __bfloat162float(a[ci]);
+            float wv = __bfloat162float(w[ci]);
+            if (p.use_lo) {
+              av += __bfloat162float(a[ci + p.in_lo_off]);
+              wv += __bfloat162float(w[plane + ci]);
+            }
+            acc = fmaf(av, wv, acc);
+          }
+        }
+    } else {
+      const int iy = oy >> 1, ix = ox >> 1, quad = (oy & 1) * 2 + (ox & 1);
+      const __nv_bfloat16* a = p.in + ((size_t)((size_t)s * p.in_H + iy) * p.in_W + ix) * p.in_pitch;
+      const __nv_bfloat16* w = p.wp + ((size_t)quad * p.cout + co) * p.cin;
+      for (int ci = 0; ci < p.cin; ++ci) {
+        float av = __bfloat162float(a[ci]);
+        float wv = __bfloat162float(w[ci]);
+        if (p.use_lo) {
+          av += __bfloat162float(a[ci + p.in_lo_off]);
+          wv += __bfloat162float(w[plane + ci]);
+        }
+        acc = fmaf(av, wv, acc);
+      }
+    }
+    float sc = p.scale[co];
+    if (p.mask) sc *= p.mask[(size_t)s * p.mask_stride + co];
+    const float y = leaky(acc * sc + (p.bias[co] * sc + p.shift[co]), p.slope);
+    __nv_bfloat16 hi, lo;
+    split_bf16(y, hi, lo);
+    __nv_bfloat16* dst = p.out + ((size_t)((size_t)s * p.out_H + oy) * p.out_W + ox) * p.out_pitch + co;
+    dst[p.out_hi_off] = hi;
+    if (p.write_lo) dst[p.out_lo_off] = lo;
+  }
+}
+
+}  // namespace b200al
