@@ -1,0 +1,149 @@
+/* libb200al - B200-native active-learning acquisition pass (C ABI).
+ *
+ * Drop-in boundary for the hot path of trnKhanh/medical-image-analysis:
+ * `ActiveSelector.select_next_batch` (src/activelearning/active_selector.py:10-19)
+ * and what it runs on a pool: the UNet forward, the per-image uncertainty
+ * reduction, rank & cut, and k-center-greedy on bottleneck embeddings.  The
+ * reference is pure Python with no FFI, so these entry points
+ * are what a ctypes binding on the reference side calls (INTEGRATION.md shows
+ * the stub).  Each one cites the reference code it replaces.
+ *
+ * Conventions: every pointer named d_* is a DEVICE pointer owned by the caller
+ * (e.g. torch-allocated); the library owns only what hangs off the opaque
+ * context.  Calls are asynchronous on `stream` (a cudaStream_t passed as
+ * void*; NULL = legacy default stream) unless stated.  Return value 0 on
+ * success, a negative b200al_status otherwise; b200al_last_error() gives the
+ * message.  There is no CPU fallback anywhere: without a sm_100 GPU the
+ * compute calls fail with B200AL_ERR_CUDA.
+ */
+#ifndef B200AL_H_
+#define B200AL_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200al_ctx b200al_ctx;
+
+enum b200al_status {
+  B200AL_OK = 0,
+  B200AL_ERR_ARG = -1,         /* bad argument / unsupported shape */
+  B200AL_ERR_CUDA = -2,        /* CUDA runtime / driver error */
+  B200AL_ERR_STATE = -3,       /* call order (e.g. weights not loaded) */
+  B200AL_ERR_UNSUPPORTED = -4  /* configuration outside the al_train UNet */
+};
+
+enum b200al_score_mode {    /* which selector's score */
+  B200AL_ENTROPY = 0,       /* EntropySelector.cal_scores     entropy_selector.py:45-49 */
+  B200AL_MARGIN = 1,        /* MarginSelector.cal_scores      margin_selector.py:45-48 */
+  B200AL_CONFIDENCE = 2     /* ConfidenceSelector.cal_scores  confidence_selector.py:45-47 */
+};
+enum b200al_metric { B200AL_L2 = 0, B200AL_COSINE = 1 }; /* CoresetSelector(metric=...) */
+enum b200al_precision {
+  B200AL_BF16X3 = 0, /* bf16 hi/lo split operands, 3 MMAs per k-step, fp32 accumulate (default; parity grade) */
+  B200AL_BF16 = 1    /* single bf16 operands (fast; does not meet the 2e-2 logit tolerance) */
+};
+enum b200al_image_dtype { B200AL_U8 = 0 /* x/255, torchvision to_tensor */, B200AL_F32 = 1 };
+
+#define B200AL_NUM_BLOCKS 18       /* PlainBlocks: 10 encoder + 8 decoder (unet.py:53-78,131-176) */
+#define B200AL_NUM_UPSAMPLES 4     /* ConvTranspose2d k2 s2 (unet.py:143-144) */
+#define B200AL_MASK_CHANNELS 2944  /* sum of Dropout2d channel counts over the 18 blocks */
+#define B200AL_EMBED_DIM 512
+
+/* One PlainBlock (blocks.py:83-102): Conv2d 3x3 (weight [Cout,Cin,3,3], bias) +
+ * BatchNorm2d running statistics and affine.  fp32 device pointers in the
+ * reference's state_dict layout (`...all.0.weight`, `...all.2.running_var`, ...). */
+typedef struct {
+  const float* d_conv_weight;
+  const float* d_conv_bias;
+  const float* d_bn_gamma;
+  const float* d_bn_beta;
+  const float* d_bn_mean;
+  const float* d_bn_var;
+} b200al_block_weights;
+
+typedef struct {
+  b200al_block_weights blocks[B200AL_NUM_BLOCKS];   /* forward order: encoder.levels.l.{0,1}, decoder.levels.l.{0,1} */
+  const float* d_up_weight[B200AL_NUM_UPSAMPLES];   /* decoder.upsamples.l.weight [Cin,Cout,2,2] */
+  const float* d_up_bias[B200AL_NUM_UPSAMPLES];
+  const float* d_head_weight;                       /* decoder.seg_output.weight [K,32,1,1] */
+  const float* d_head_bias;                         /* [K] */
+  float bn_eps;                                     /* 1e-5  (blocks.py:98) */
+  float leaky_slope;                                /* 0.01  (blocks.py:100) */
+} b200al_weights;
+
+/* Context for one device.  num_out = output classes K (num_classes+1,
+ * al_trainer.py:508), in_channels must be 1, H = W = multiple of 128
+ * (256 after JointResize, entry/activelearning/train.py:30), max_samples =
+ * largest number of (image x MC repeat) samples forwarded per call chunk. */
+int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int in_channels, int H, int W, int max_samples,
+                      int precision);
+void b200al_ctx_destroy(b200al_ctx* ctx);
+const char* b200al_last_error(const b200al_ctx* ctx); /* ctx may be NULL: last global error */
+
+/* Fold BatchNorm and pack weights for the tensor-core kernels, on device.
+ * Replaces reading `model.state_dict()` each round (al_trainer.py:1048-1083). */
+int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, void* stream);
+
+/* Score n pool images: UNet.forward (unet.py:293) + the selector's per-image
+ * score, T >= 1 MC-dropout repeats (T == 1 and drop_p == 0: plain eval mode,
+ * exactly the reference selectors).  d_images: [n,H,W] u8 or f32.
+ * MC masks: d_drop_masks ([n,T,2944] multipliers, 0 or 1/(1-p)) if non-NULL,
+ * else generated from (mc_seed, base_pos + i, t, channel) - see oracle/synth.py.
+ * d_scores_out [n] fp32.  d_logits_out nullable: [n*T, K, H, W] fp32.
+ * n*T must be <= max_samples. */
+int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int image_dtype, int n, int mode, int T, float drop_p,
+                       uint64_t mc_seed, int64_t base_pos, const float* d_drop_masks, float smooth,
+                       float* d_scores_out, float* d_logits_out, void* stream);
+
+/* UNet.get_enc_feature (unet.py:296-297, 89-93): encoder + global average pool.
+ * d_emb_out [n,512] fp32.  n <= max_samples. */
+int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, int n, float* d_emb_out, void* stream);
+
+/* Kernel 3 alone: scores from fp32 logits [n,T,K,HW] already in HBM
+ * (softmax -> mean over T -> entropy / margin / confidence -> mean over pixels). */
+int b200al_uncertainty_from_logits(b200al_ctx* ctx, const float* d_logits, int n, int T, int K, int HW, int mode,
+                                   float smooth, float* d_scores_out, void* stream);
+
+/* Rank & cut (entropy_selector.py:76-82): k best of n scores, descending,
+ * ties -> lower position first.  Writes k' = min(k,n) entries; positions are
+ * base_pos + index.  d_out_scores [k'], d_out_pos [k'] int64. */
+int b200al_topk(b200al_ctx* ctx, const float* d_scores, int n, int k, int64_t base_pos, float* d_out_scores,
+                int64_t* d_out_pos, void* stream);
+
+/* k-center greedy (coreset_selector.py:19-51, criteria "min").
+ * init: d_mind[i] = min_j dist(emb_i, centre_j) over L centres (the labeled
+ * rows, coreset_selector.py:85,226); accumulate != 0 folds into existing mind.
+ * For COSINE both matrices must hold rows normalised by b200al_normalize_rows. */
+int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, int D, const float* d_centres, int L, int metric,
+                        float* d_mind, int accumulate, void* stream);
+/* run: `budget` greedy steps over rows not marked in d_taken (uint8 [n]);
+ * d_picks [budget] int64 row indices in selection order (-1 when exhausted),
+ * d_pick_vals nullable [budget] = the max-min distance of each pick.
+ * d_mind / d_taken are updated in place. */
+int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, float* d_mind, uint8_t* d_taken,
+                       int budget, int64_t* d_picks, float* d_pick_vals, void* stream);
+int b200al_normalize_rows(b200al_ctx* ctx, const float* d_in, float* d_out, int n, int D, void* stream);
+
+/* Introspection for benches / tests. */
+int b200al_kernel_launches(const b200al_ctx* ctx, int64_t* out_count);      /* kernels launched so far */
+/* CUDA-event timing around every tcgen05 conv launch (up to 32768 launches
+ * between two b200al_conv_time_ms calls).  conv_time_ms synchronises the
+ * device and returns the summed kernel time, the number of timed launches and
+ * their algorithmic FLOPs (2*MAC, single-precision-equivalent). */
+int b200al_set_timing(b200al_ctx* ctx, int enable);
+int b200al_conv_time_ms(b200al_ctx* ctx, float* out_ms, int64_t* out_launches, double* out_flops);
+
+/* TEST HOOKS (not part of the drop-in surface): run ONE 3x3 conv / transposed
+ * conv layer of the loaded model on caller-provided NHWC hi/lo activations,
+ * with the tcgen05 kernel (impl 0) or the SIMT cross-check kernel (impl 1). */
+int b200al_debug_layer(b200al_ctx* ctx, int layer_index, int impl, const void* d_in, void* d_out, int n_samples,
+                       const float* d_mask, void* stream);
+int b200al_debug_layer_info(b200al_ctx* ctx, int layer_index, int* info /*[12]*/);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200AL_H_ */

@@ -1,0 +1,72 @@
+"""Pool sharding across ranks (one process per GPU, torch.distributed).
+
+The reference is single-process; sharding is new.  Images are
+independent on the scoring path (entropy_selector.py:38-52 has no cross-image
+term, BatchNorm is in eval mode), so the pool is cut into contiguous position
+ranges with NO data-path collective; only per-shard top-k candidates
+(score fp32, position int64) or embedding rows are exchanged:
+
+  uncertainty: all_gather of each rank's top-min(k, n_r) (score, pos) pairs,
+               every rank merges identically (score desc, position asc).
+  coreset:     all_gather of embedding rows [n_r, 512]; k-center then runs
+               replicated on every rank (500 greedy steps are latency-bound:
+               a per-step collective would cost more than the whole loop).
+
+Works with the gloo backend on CPU tensors (tests) and nccl on CUDA tensors.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+def world():
+    if dist.is_available() and dist.is_initialized():
+        return dist.get_rank(), dist.get_world_size()
+    return 0, 1
+
+
+def shard_range(n: int, rank: int, world_size: int) -> tuple[int, int]:
+    """Contiguous [lo, hi) of rank `rank`: floor(r*n/W) .. floor((r+1)*n/W)."""
+    return (rank * n) // world_size, ((rank + 1) * n) // world_size
+
+
+def merge_topk(scores: torch.Tensor, pos: torch.Tensor, k: int):
+    """Exact merge of candidate lists: descending score, ascending position."""
+    if scores.numel() == 0:
+        return scores, pos
+    # two stable sorts: by position, then by score descending
+    o = torch.argsort(pos, stable=True)
+    scores, pos = scores[o], pos[o]
+    o = torch.argsort(scores, descending=True, stable=True)
+    return scores[o][:k], pos[o][:k]
+
+
+def all_gather_varlen(t: torch.Tensor, group=None) -> torch.Tensor:
+    """Concatenate per-rank tensors of differing first dimension (rank order)."""
+    rank, ws = world()
+    if ws == 1:
+        return t
+    n = torch.tensor([t.shape[0]], dtype=torch.int64, device=t.device)
+    sizes = [torch.zeros_like(n) for _ in range(ws)]
+    dist.all_gather(sizes, n, group=group)
+    sizes = [int(s.item()) for s in sizes]
+    mx = max(sizes)
+    pad = torch.zeros((mx,) + tuple(t.shape[1:]), dtype=t.dtype, device=t.device)
+    pad[: t.shape[0]] = t
+    bufs = [torch.empty_like(pad) for _ in range(ws)]
+    dist.all_gather(bufs, pad, group=group)
+    return torch.cat([b[:s] for b, s in zip(bufs, sizes)], 0)
+
+
+def global_topk(local_scores: torch.Tensor, local_pos: torch.Tensor, k: int, group=None):
+    """local_* = this rank's own top-min(k, n_r) candidates with GLOBAL pool
+    positions.  Returns the global top-k, identical on every rank."""
+    s = all_gather_varlen(local_scores, group)
+    p = all_gather_varlen(local_pos, group)
+    return merge_topk(s, p, k)
+
+
+def gather_rows(local_rows: torch.Tensor, group=None) -> torch.Tensor:
+    """All ranks' rows in rank (== pool position) order."""
+    return all_gather_varlen(local_rows, group)

@@ -1,0 +1,330 @@
+"""Device-side engine: owns a libb200al context, ingests UNet weights from a
+live `nn.Module.state_dict()` (reference key layout) and runs the
+scoring / embedding / rank / k-center calls.  torch is used for device memory
+and streams only; all arithmetic happens in the CUDA library.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Mapping
+
+import torch
+
+from . import _lib
+
+CHANNELS = (32, 64, 128, 256, 512)
+
+
+def block_prefixes():
+    """state_dict prefixes of the 18 PlainBlocks in forward order
+    (src/models/unet/unet.py:53-78,131-176)."""
+    out = []
+    for l in range(5):
+        out += [f"encoder.levels.{l}.0.all", f"encoder.levels.{l}.1.all"]
+    for l in range(4):
+        out += [f"decoder.levels.{l}.0.all", f"decoder.levels.{l}.1.all"]
+    return out
+
+
+def block_channels():
+    c = []
+    for l in range(5):
+        c += [CHANNELS[l], CHANNELS[l]]
+    for l in range(4):
+        c += [CHANNELS[3 - l], CHANNELS[3 - l]]
+    return c
+
+
+def validate_state_dict(sd: Mapping[str, torch.Tensor]) -> int:
+    """Checks that `sd` is the al_train UNet (2D, plain blocks, BatchNorm,
+    transposed-conv upsampling, no deep supervision, 1 input channel) and
+    returns K.  Anything else raises NotImplementedError (no silent fallback)."""
+    if any(".downsample_skip." in k for k in sd):
+        raise NotImplementedError("residual blocks (block_type='res') are not supported")
+    if any(k.startswith("decoder.ds.") for k in sd):
+        raise NotImplementedError("deep-supervision heads are not supported")
+    pre = block_prefixes()
+    chans = block_channels()
+    cin = [1] + [chans[i - 1] for i in range(1, 10)] + [0] * 8
+    for l in range(4):
+        cin[10 + 2 * l] = 2 * CHANNELS[3 - l]
+        cin[11 + 2 * l] = CHANNELS[3 - l]
+    for i, p in enumerate(pre):
+        w = sd.get(f"{p}.0.weight")
+        if w is None:
+            raise NotImplementedError(f"missing {p}.0.weight: not the al_train UNet ([32,64,128,256,512], plain)")
+        if w.dim() != 4:
+            raise NotImplementedError("3D UNet is not supported")
+        if f"{p}.2.running_mean" not in sd:
+            raise NotImplementedError("normalization must be 'batch' (InstanceNorm has no running statistics to fold)")
+        if tuple(w.shape) != (chans[i], cin[i], 3, 3):
+            if i == 0 and w.shape[1] != 1:
+                raise NotImplementedError(f"in_channels={w.shape[1]}: only grayscale (1) is supported")
+            raise NotImplementedError(f"{p}.0.weight has shape {tuple(w.shape)}, expected {(chans[i], cin[i], 3, 3)}")
+    for l in range(4):
+        w = sd.get(f"decoder.upsamples.{l}.weight")
+        if w is None or tuple(w.shape) != (CHANNELS[4 - l], CHANNELS[3 - l], 2, 2):
+            raise NotImplementedError("upsampling must be ConvTranspose2d(k=2, s=2) (upconv=True)")
+    hw = sd.get("decoder.seg_output.weight")
+    if hw is None or hw.dim() != 4 or hw.shape[1] != 32 or hw.shape[2:] != (1, 1):
+        raise NotImplementedError("decoder.seg_output must be a 1x1 conv on 32 channels")
+    return int(hw.shape[0])
+
+
+def module_hparams(model) -> tuple[float, float, float | None]:
+    """(bn_eps, leaky_slope, dropout_p) read from the live module when it is
+    one; the reference's defaults otherwise (blocks.py:98,100)."""
+    eps, slope, p = 1e-5, 0.01, None
+    mods = getattr(model, "modules", None)
+    if callable(mods):
+        for m in model.modules():
+            if isinstance(m, torch.nn.BatchNorm2d):
+                eps = float(m.eps)
+            elif isinstance(m, torch.nn.LeakyReLU):
+                slope = float(m.negative_slope)
+            elif isinstance(m, torch.nn.Dropout2d) and p is None:
+                p = float(m.p)
+    return eps, slope, p
+
+
+class Engine:
+    """One context per (device, K, H, W, max_samples, precision)."""
+
+    def __init__(self, device, num_out: int, H: int = 256, W: int = 256, max_samples: int = 64,
+                 precision: str = "bf16x3"):
+        self.lib = _lib.load()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("b200al runs on a CUDA (sm_100a) device only; there is no CPU path")
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", idx)
+        self.K, self.H, self.W, self.max_samples = num_out, H, W, max_samples
+        self.precision = precision
+        ctx = C.c_void_p()
+        _lib.check(self.lib.b200al_ctx_create(C.byref(ctx), idx, num_out, 1, H, W, max_samples,
+                                              _lib.PRECISIONS[precision]))
+        self.ctx = ctx
+        self._keep = []          # device tensors the loaded weights point at
+        self.dropout_p = None
+
+    def close(self):
+        if getattr(self, "ctx", None):
+            self.lib.b200al_ctx_destroy(self.ctx)
+            self.ctx = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ------------------------------------------------------------------ utils
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    @staticmethod
+    def _ptr(t):
+        return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+    def _check(self, rc):
+        _lib.check(rc, self.ctx)
+
+    # ---------------------------------------------------------------- weights
+    def load_model(self, model) -> None:
+        """Fold + pack the weights of `model` (nn.Module with the reference
+        UNet's state_dict layout, or a plain state_dict)."""
+        sd = model.state_dict() if hasattr(model, "state_dict") else model
+        K = validate_state_dict(sd)
+        if K != self.K:
+            raise ValueError(f"model has {K} output classes, engine was created for {self.K}")
+        eps, slope, p = module_hparams(model)
+        self.dropout_p = p
+
+        def dev(name):
+            t = sd[name].detach().to(device=self.device, dtype=torch.float32).contiguous()
+            self._keep.append(t)
+            return C.c_void_p(t.data_ptr())
+
+        self._keep = []
+        w = _lib.Weights()
+        for i, pre in enumerate(block_prefixes()):
+            b = w.blocks[i]
+            b.d_conv_weight = dev(f"{pre}.0.weight")
+            b.d_conv_bias = dev(f"{pre}.0.bias")
+            b.d_bn_gamma = dev(f"{pre}.2.weight")
+            b.d_bn_beta = dev(f"{pre}.2.bias")
+            b.d_bn_mean = dev(f"{pre}.2.running_mean")
+            b.d_bn_var = dev(f"{pre}.2.running_var")
+        for l in range(4):
+            w.d_up_weight[l] = dev(f"decoder.upsamples.{l}.weight")
+            w.d_up_bias[l] = dev(f"decoder.upsamples.{l}.bias")
+        w.d_head_weight = dev("decoder.seg_output.weight")
+        w.d_head_bias = dev("decoder.seg_output.bias")
+        w.bn_eps = eps
+        w.leaky_slope = slope
+        with torch.cuda.device(self.device):
+            self._check(self.lib.b200al_load_weights(self.ctx, C.byref(w), self._stream()))
+
+    # ---------------------------------------------------------------- scoring
+    def _images(self, images: torch.Tensor):
+        if images.device != self.device:
+            raise ValueError(f"images must live on {self.device}")
+        if images.dim() == 4:
+            if images.shape[1] != 1:
+                raise NotImplementedError("only 1-channel images are supported")
+            images = images[:, 0]
+        if images.shape[-2:] != (self.H, self.W):
+            raise ValueError(f"images must be {self.H}x{self.W}, got {tuple(images.shape[-2:])}")
+        if images.dtype == torch.uint8:
+            return images.contiguous(), _lib.U8
+        if images.dtype == torch.float32:
+            return images.contiguous(), _lib.F32
+        raise TypeError(f"image dtype {images.dtype} not supported (uint8 or float32)")
+
+    def scores(self, images: torch.Tensor, mode: str = "entropy", T: int = 1, drop_p: float = 0.0, seed: int = 0,
+               base_pos: int = 0, masks: torch.Tensor | None = None, smooth: float = 1e-8,
+               return_logits: bool = False):
+        """Per-image scores [n] (fp32, on device) for device-resident images
+        [n,H,W] / [n,1,H,W]; chunks internally to max_samples // T images."""
+        imgs, dt = self._images(images)
+        n = imgs.shape[0]
+        out = torch.empty(n, dtype=torch.float32, device=self.device)
+        logits = torch.empty((n * T, self.K, self.H, self.W), dtype=torch.float32, device=self.device) \
+            if return_logits else None
+        per = max(1, self.max_samples // T)
+        if T > self.max_samples:
+            raise ValueError(f"T={T} exceeds max_samples={self.max_samples}")
+        if masks is not None:
+            masks = masks.to(device=self.device, dtype=torch.float32).contiguous()
+            if tuple(masks.shape) != (n, T, _lib.MASK_CHANNELS):
+                raise ValueError(f"masks must be [n,T,{_lib.MASK_CHANNELS}]")
+        st = self._stream()
+        with torch.cuda.device(self.device):
+            for i in range(0, n, per):
+                m = min(per, n - i)
+                self._check(self.lib.b200al_unet_scores(
+                    self.ctx, self._ptr(imgs[i:i + m]), dt, m, _lib.MODES[mode], T, float(drop_p), int(seed),
+                    int(base_pos + i), self._ptr(masks[i:i + m] if masks is not None else None), float(smooth),
+                    self._ptr(out[i:i + m]), self._ptr(logits[i * T:(i + m) * T] if logits is not None else None), st))
+        return (out, logits) if return_logits else out
+
+    def embed(self, images: torch.Tensor) -> torch.Tensor:
+        """UNet.get_enc_feature: [n,512] fp32 on device."""
+        imgs, dt = self._images(images)
+        n = imgs.shape[0]
+        out = torch.empty((n, _lib.EMBED_DIM), dtype=torch.float32, device=self.device)
+        st = self._stream()
+        with torch.cuda.device(self.device):
+            for i in range(0, n, self.max_samples):
+                m = min(self.max_samples, n - i)
+                self._check(self.lib.b200al_unet_embed(self.ctx, self._ptr(imgs[i:i + m]), dt, m,
+                                                       self._ptr(out[i:i + m]), st))
+        return out
+
+    def uncertainty_from_logits(self, logits: torch.Tensor, mode: str = "entropy", smooth: float = 1e-8):
+        """logits [n,K,H,W] or [n,T,K,H,W] fp32 on device -> scores [n]."""
+        if logits.dim() == 4:
+            logits = logits.unsqueeze(1)
+        n, T, K = logits.shape[:3]
+        hw = logits.shape[3] * logits.shape[4]
+        logits = logits.to(torch.float32).contiguous()
+        out = torch.empty(n, dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.b200al_uncertainty_from_logits(self.ctx, self._ptr(logits), n, T, K, hw,
+                                                                _lib.MODES[mode], float(smooth), self._ptr(out),
+                                                                self._stream()))
+        return out
+
+    # ------------------------------------------------------------ rank & cut
+    def topk(self, scores: torch.Tensor, k: int, base_pos: int = 0):
+        """k best (descending score, lower position on ties): (scores[k'], pos[k'] int64)."""
+        scores = scores.to(device=self.device, dtype=torch.float32).contiguous()
+        n = scores.numel()
+        k = min(int(k), n)
+        vals = torch.empty(k, dtype=torch.float32, device=self.device)
+        pos = torch.empty(k, dtype=torch.int64, device=self.device)
+        if k:
+            with torch.cuda.device(self.device):
+                self._check(self.lib.b200al_topk(self.ctx, self._ptr(scores), n, k, int(base_pos), self._ptr(vals),
+                                                 self._ptr(pos), self._stream()))
+        return vals, pos
+
+    # --------------------------------------------------------------- k-center
+    def kcenter(self, feats: torch.Tensor, n_init: int, budget: int, metric: str = "l2", return_vals: bool = False):
+        """k-center greedy over rows of `feats` [n,D] (fp32, device); rows
+        [0,n_init) are the initial centres (labeled set).  Returns row indices
+        (int64, selection order)."""
+        feats = feats.to(device=self.device, dtype=torch.float32).contiguous()
+        n, D = feats.shape
+        if n_init < 1:
+            raise ValueError("k-center needs at least one labeled row (the reference falls back to random selection)")
+        budget = min(int(budget), n - n_init)
+        picks = torch.empty(budget, dtype=torch.int64, device=self.device)
+        vals = torch.empty(budget, dtype=torch.float32, device=self.device)
+        if budget <= 0:
+            return (picks, vals) if return_vals else picks
+        st = self._stream()
+        m = _lib.METRICS[metric]
+        with torch.cuda.device(self.device):
+            if metric == "cosine":
+                normed = torch.empty_like(feats)
+                self._check(self.lib.b200al_normalize_rows(self.ctx, self._ptr(feats), self._ptr(normed), n, D, st))
+                feats = normed
+            mind = torch.empty(n, dtype=torch.float32, device=self.device)
+            taken = torch.zeros(n, dtype=torch.uint8, device=self.device)
+            taken[:n_init] = 1
+            self._check(self.lib.b200al_kcenter_init(self.ctx, self._ptr(feats), n, D, self._ptr(feats), n_init, m,
+                                                     self._ptr(mind), 0, st))
+            self._check(self.lib.b200al_kcenter_run(self.ctx, self._ptr(feats), n, D, m, self._ptr(mind),
+                                                    self._ptr(taken), budget, self._ptr(picks), self._ptr(vals), st))
+        return (picks, vals) if return_vals else picks
+
+    # ---------------------------------------------------------- introspection
+    def kernel_launches(self) -> int:
+        c = C.c_int64()
+        self._check(self.lib.b200al_kernel_launches(self.ctx, C.byref(c)))
+        return c.value
+
+    def set_timing(self, enable: bool):
+        self._check(self.lib.b200al_set_timing(self.ctx, int(enable)))
+
+    def conv_time_ms(self):
+        """(summed tcgen05 conv kernel ms, timed launches, their FLOPs) since set_timing(True)."""
+        ms, n, fl = C.c_float(), C.c_int64(), C.c_double()
+        self._check(self.lib.b200al_conv_time_ms(self.ctx, C.byref(ms), C.byref(n), C.byref(fl)))
+        return ms.value, n.value, fl.value
+
+    # -------------------------------------------------------------- test hook
+    def debug_layer_info(self, i: int):
+        arr = (C.c_int * 12)()
+        self._check(self.lib.b200al_debug_layer_info(self.ctx, i, arr))
+        keys = ("kind", "cin", "cout", "stride", "inH", "inW", "in_pitch", "in_c_off", "outH", "outW", "out_pitch",
+                "out_c_off")
+        return dict(zip(keys, list(arr)))
+
+    def debug_layer(self, i: int, impl: int, x: torch.Tensor, out: torch.Tensor, mask: torch.Tensor | None = None):
+        with torch.cuda.device(self.device):
+            self._check(self.lib.b200al_debug_layer(self.ctx, i, impl, self._ptr(x), self._ptr(out), x.shape[0],
+                                                    self._ptr(mask), self._stream()))
+
+
+# FLOPs per sample of the tensor-core layers (2*MAC; SURVEY.md 8a'), H=W=256
+def conv_flops_per_sample(H: int = 256, W: int = 256, encoder_only: bool = False) -> float:
+    f = 0.0
+    px = H * W
+    ch = CHANNELS
+    f += 2.0 * px * 32 * 32 * 9                      # enc0.1
+    for l in range(1, 5):
+        px_l = px // (4 ** l)
+        f += 2.0 * px_l * ch[l] * ch[l - 1] * 9      # stride-2 conv
+        f += 2.0 * px_l * ch[l] * ch[l] * 9
+    if encoder_only:
+        return f
+    for l in range(4):
+        cin, cout = ch[4 - l], ch[3 - l]
+        px_in = px // (4 ** (4 - l))
+        f += 2.0 * px_in * 4 * cout * cin            # transposed conv
+        px_out = px_in * 4
+        f += 2.0 * px_out * cout * (2 * cout) * 9
+        f += 2.0 * px_out * cout * cout * 9
+    return f

@@ -1,0 +1,32 @@
+"""Hook the drop-in selectors into the reference's trainer without editing it.
+
+`ALTrainer._setup_active_selector` (src/training/al_trainer.py:802-883) picks a
+selector by `config.active_selector_name` and raises ValueError for unknown
+names.  `install_into_al_trainer(ALTrainer)` wraps that method so the names in
+`b200al.SELECTORS` ("b200-entropy", "b200-coreset-l2", ...) construct the
+B200 selectors with the same kwargs the reference passes (batch_size,
+num_workers, pin_memory); every other name goes to the original method.
+"""
+from __future__ import annotations
+
+
+def install_into_al_trainer(trainer_cls, reference_abc=None):
+    from .selectors import SELECTORS, ActiveSelector
+
+    original = trainer_cls._setup_active_selector
+
+    def _setup_active_selector(self):
+        name = self.config.active_selector_name
+        if name in SELECTORS:
+            self.active_selector = SELECTORS[name](
+                batch_size=self.config.batch_size,
+                num_workers=self.config.num_workers,
+                pin_memory=self.config.pin_memory,
+            )
+        else:
+            original(self)
+
+    trainer_cls._setup_active_selector = _setup_active_selector
+    if reference_abc is not None:  # make isinstance(sel, reference ActiveSelector) hold
+        reference_abc.register(ActiveSelector)
+    return trainer_cls

@@ -1,0 +1,300 @@
+"""Drop-in selection strategies with the reference's plugin interface.
+
+Mirrors `ActiveSelector.select_next_batch(active_dataset, select_num, model,
+device) -> list[case_name]` (src/activelearning/active_selector.py:10-19) and
+the constructor kwargs `ALTrainer._setup_active_selector` passes
+(src/training/al_trainer.py:802-844).  Scores, embeddings, rank & cut and
+k-center all run in libb200al on the GPU; Python only moves pool chunks to the
+device and maps positions back to case names.
+
+Objects consumed (duck-typed, reference types or mirrors): `active_dataset`
+with get_size / get_pool_dataset / get_train_dataset; datasets with
+`.image_idx: list[str]` and `__getitem__ -> {"image": float32 [1,H,W], ...}`.
+Fast path: if the wrapped base dataset exposes `images_u8` ([N,H,W] uint8
+tensor, CPU or CUDA) and `names`, chunks are sliced from it directly instead of
+going through a DataLoader.
+"""
+from __future__ import annotations
+
+from abc import ABC, abstractmethod
+from typing import Any, Iterator
+
+import torch
+
+from . import dist as D
+from .engine import Engine, validate_state_dict
+
+
+class ActiveSelector(ABC):
+    """Same abstract interface as the reference's ActiveSelector."""
+
+    @abstractmethod
+    def select_next_batch(self, active_dataset, select_num: int, model, device) -> list[Any]:
+        ...
+
+
+_ENGINES: dict = {}
+
+
+def get_engine(device, num_out: int, H: int, W: int, precision: str, max_samples: int) -> Engine:
+    device = torch.device(device)
+    idx = device.index if device.index is not None else torch.cuda.current_device()
+    key = (idx, num_out, H, W, precision, max_samples)
+    eng = _ENGINES.get(key)
+    if eng is None:
+        eng = _ENGINES[key] = Engine(torch.device("cuda", idx), num_out, H, W, max_samples, precision)
+    return eng
+
+
+def _cold_start(active_dataset, select_num: int) -> list:
+    """labeled_size == 0 branch, verbatim call sequence so the seeded global
+    CPU RNG stream matches the reference (entropy_selector.py:64-71)."""
+    _, pool_size = active_dataset.get_size()
+    scores = torch.rand(pool_size)
+    _, indices = torch.sort(scores, descending=True)
+    return [active_dataset.pool_dataset.image_idx[id] for id in indices[:select_num]]
+
+
+class PoolSource:
+    """Feeds device-resident image chunks of a dataset in position order."""
+
+    def __init__(self, dataset, device, batch_size: int, num_workers: int, pin_memory: bool):
+        self.ds, self.device = dataset, torch.device(device)
+        self.batch_size, self.num_workers, self.pin_memory = batch_size, num_workers, pin_memory
+        base = getattr(dataset, "dataset", None)
+        self.resident = None
+        if base is not None and hasattr(base, "images_u8") and hasattr(dataset, "case_name_to_idx"):
+            self.resident = base.images_u8
+
+    def image_hw(self) -> tuple[int, int]:
+        if self.resident is not None:
+            return tuple(self.resident.shape[-2:])
+        if len(self.ds) == 0:
+            return (256, 256)
+        return tuple(self.ds[0]["image"].shape[-2:])
+
+    def chunks(self, positions: list[int], chunk: int) -> Iterator[tuple[int, torch.Tensor]]:
+        """Yields (offset into `positions`, images on device) with one chunk of
+        host->device copy in flight ahead of the consumer."""
+        if not positions:
+            return
+        if self.resident is not None:
+            rows = torch.tensor([self.ds.case_name_to_idx[self.ds.image_idx[p]] for p in positions], dtype=torch.int64)
+            if self.resident.is_cuda:
+                rows = rows.to(self.resident.device)
+                for i in range(0, len(positions), chunk):
+                    yield i, self.resident.index_select(0, rows[i:i + chunk]).to(self.device)
+                return
+            copy_stream = torch.cuda.Stream(self.device)
+            cur = torch.cuda.current_stream(self.device)
+            contiguous = bool((rows[1:] - rows[:-1] == 1).all()) if len(rows) > 1 else True
+
+            def stage(i):
+                if contiguous:
+                    host = self.resident[int(rows[i]): int(rows[i]) + len(rows[i:i + chunk])]
+                else:
+                    host = self.resident.index_select(0, rows[i:i + chunk])
+                if not host.is_pinned() and self.pin_memory:
+                    host = host.pin_memory()
+                with torch.cuda.stream(copy_stream):
+                    dev = host.to(self.device, non_blocking=True)
+                    ev = torch.cuda.Event()
+                    ev.record(copy_stream)
+                return dev, ev, host
+
+            nxt = stage(0)
+            for i in range(0, len(positions), chunk):
+                dev, ev, _host = nxt
+                if i + chunk < len(positions):
+                    nxt = stage(i + chunk)
+                cur.wait_event(ev)
+                dev.record_stream(cur)
+                yield i, dev
+            return
+        # generic path: the reference's own DataLoader settings (entropy_selector.py:30-35)
+        from torch.utils.data import DataLoader, Subset
+        loader = DataLoader(Subset(self.ds, positions), batch_size=min(chunk, max(1, self.batch_size)),
+                            num_workers=self.num_workers, pin_memory=self.pin_memory)
+        off = 0
+        for batch in loader:
+            img = batch["image"].to(self.device, non_blocking=True).to(torch.float32)
+            yield off, img
+            off += img.shape[0]
+
+
+class _B200Base(ActiveSelector):
+    def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8, *,
+                 precision: str = "bf16x3", chunk_samples: int = 64):
+        self.batch_size, self.num_workers, self.pin_memory = batch_size, num_workers, pin_memory
+        self.smooth = smooth
+        self.precision = precision
+        self.chunk_samples = chunk_samples
+
+    def _engine(self, model, device, hw) -> Engine:
+        sd = model.state_dict()
+        K = validate_state_dict(sd)
+        eng = get_engine(device, K, hw[0], hw[1], self.precision, self.chunk_samples)
+        model.eval()  # the reference's own side effect (entropy_selector.py:42)
+        eng.load_model(model)  # every call: the trainer rebuilds / reloads the model each round
+        return eng
+
+
+class _B200Uncertainty(_B200Base):
+    mode = "entropy"
+
+    def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8, *,
+                 mc_repeats: int = 1, dropout_prob: float | None = None, mc_seed: int = 0, **kw):
+        super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
+        self.mc_repeats, self.dropout_prob, self.mc_seed = int(mc_repeats), dropout_prob, int(mc_seed)
+
+    def _score_positions(self, eng: Engine, src: PoolSource, positions: list[int]):
+        T = self.mc_repeats
+        p = 0.0
+        if T > 1:
+            p = self.dropout_prob if self.dropout_prob is not None else (eng.dropout_p or 0.0)
+        out = torch.empty(len(positions), dtype=torch.float32, device=eng.device)
+        per = max(1, eng.max_samples // T)
+        for off, imgs in src.chunks(positions, per):
+            # MC masks are keyed by pool position so any sharding gives the same scores
+            out[off:off + imgs.shape[0]] = eng.scores(imgs, self.mode, T=T, drop_p=p, seed=self.mc_seed,
+                                                      base_pos=positions[off], smooth=self.smooth)
+        return out
+
+    def _scores_local(self, active_dataset, model, device):
+        pool = active_dataset.get_pool_dataset()
+        rank, ws = D.world()
+        lo, hi = D.shard_range(len(pool), rank, ws)
+        src = PoolSource(pool, device, self.batch_size, self.num_workers, self.pin_memory)
+        eng = self._engine(model, device, src.image_hw())
+        return eng, self._score_positions(eng, src, list(range(lo, hi))), lo, hi
+
+    def cal_scores(self, active_dataset, model, device):
+        """(scores [device tensor], case names) of this rank's pool shard, in
+        pool order - the whole pool when not distributed, like the reference's
+        cal_scores (entropy_selector.py:24-54)."""
+        _eng, scores, lo, hi = self._scores_local(active_dataset, model, device)
+        return scores, active_dataset.get_pool_dataset().image_idx[lo:hi]
+
+    def select_next_batch(self, active_dataset, select_num: int, model, device):
+        labeled_size, pool_size = active_dataset.get_size()
+        if labeled_size == 0:
+            return _cold_start(active_dataset, select_num)
+        eng, scores, lo, _hi = self._scores_local(active_dataset, model, device)
+        vals, pos = eng.topk(scores, select_num, base_pos=lo)
+        if D.world()[1] > 1:
+            vals, pos = D.global_topk(vals, pos, select_num)
+        names = active_dataset.get_pool_dataset().image_idx
+        return [names[p] for p in pos.tolist()]
+
+
+class B200EntropySelector(_B200Uncertainty):
+    """EntropySelector (src/activelearning/entropy_selector.py:11)."""
+    mode = "entropy"
+
+
+class B200MarginSelector(_B200Uncertainty):
+    """MarginSelector (src/activelearning/margin_selector.py:11)."""
+    mode = "margin"
+
+
+class B200ConfidenceSelector(_B200Uncertainty):
+    """ConfidenceSelector (src/activelearning/confidence_selector.py:11)."""
+    mode = "confidence"
+
+
+class B200MCDropoutEntropySelector(_B200Uncertainty):
+    """Entropy of the mean of T MC-dropout softmax maps (not in the reference;
+    composed from its UNet + Dropout2d + entropy formula)."""
+    mode = "entropy"
+
+    def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8, *,
+                 mc_repeats: int = 8, **kw):
+        super().__init__(batch_size, num_workers, pin_memory, smooth, mc_repeats=mc_repeats, **kw)
+
+
+def _embed_positions(eng: Engine, src: PoolSource, positions: list[int]) -> torch.Tensor:
+    out = torch.empty((len(positions), 512), dtype=torch.float32, device=eng.device)
+    for off, imgs in src.chunks(positions, eng.max_samples):
+        out[off:off + imgs.shape[0]] = eng.embed(imgs)
+    return out
+
+
+class B200CoresetSelector(_B200Base):
+    """CoresetSelector (src/activelearning/coreset_selector.py:54) for
+    metric in {l2, cosine}, coreset_criteria 'min', model features only."""
+
+    def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8,
+                 metric: str = "cosine", coreset_criteria: str = "min", coreset_fusion: str = "add",
+                 feature_path=None, loaded_feature_weight: float = 0.0, **kw):
+        super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
+        if metric not in ("l2", "cosine"):
+            raise NotImplementedError(f"metric {metric!r}: only 'l2' and 'cosine' are supported")
+        if coreset_criteria != "min":
+            if coreset_criteria == "mean":
+                raise NotImplementedError("coreset_criteria='mean' is not supported yet")
+            raise RuntimeError(f"coreset_criteria {coreset_criteria} is undefined")  # coreset_selector.py:38-40
+        if feature_path is not None or loaded_feature_weight != 0.0:
+            raise NotImplementedError("externally loaded features (feature_path / loaded_feature_weight) are not supported")
+        self.metric = metric
+
+    def select_next_batch(self, active_dataset, select_num: int, model, device):
+        labeled_size, pool_size = active_dataset.get_size()
+        if labeled_size == 0:
+            return _cold_start(active_dataset, select_num)  # coreset_selector.py:193-200
+        labeled, pool = active_dataset.get_train_dataset(), active_dataset.get_pool_dataset()
+        all_list = list(labeled.image_idx) + list(pool.image_idx)  # labeled rows first (coreset_selector.py:85-88)
+        rank, ws = D.world()
+        lo, hi = D.shard_range(pool_size, rank, ws)
+        psrc = PoolSource(pool, device, self.batch_size, self.num_workers, self.pin_memory)
+        lsrc = PoolSource(labeled, device, self.batch_size, self.num_workers, self.pin_memory)
+        eng = self._engine(model, device, psrc.image_hw())
+        emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
+        emb_p = D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi))))
+        feats = torch.cat([emb_l, emb_p], 0)
+        picks = eng.kcenter(feats, labeled_size, select_num, self.metric)
+        return [all_list[i] for i in picks.tolist()]
+
+
+class B200HybridSelector(_B200Uncertainty):
+    """Uncertainty pre-filter (top `prefilter_factor * select_num` by score)
+    followed by k-center greedy (l2) on the survivors' embeddings.  Not in the
+    reference; composed from its cal_scores and kcenter_greedy."""
+
+    def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8, *,
+                 mode: str = "entropy", prefilter_factor: int = 10, **kw):
+        super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
+        self.mode = mode
+        self.prefilter_factor = int(prefilter_factor)
+
+    def select_next_batch(self, active_dataset, select_num: int, model, device):
+        labeled_size, pool_size = active_dataset.get_size()
+        if labeled_size == 0:
+            return _cold_start(active_dataset, select_num)
+        labeled, pool = active_dataset.get_train_dataset(), active_dataset.get_pool_dataset()
+        rank, ws = D.world()
+        lo, hi = D.shard_range(pool_size, rank, ws)
+        psrc = PoolSource(pool, device, self.batch_size, self.num_workers, self.pin_memory)
+        lsrc = PoolSource(labeled, device, self.batch_size, self.num_workers, self.pin_memory)
+        eng = self._engine(model, device, psrc.image_hw())
+        scores = self._score_positions(eng, psrc, list(range(lo, hi)))
+        m = min(pool_size, self.prefilter_factor * select_num)
+        vals, pos = eng.topk(scores, m, base_pos=lo)
+        if ws > 1:
+            vals, pos = D.global_topk(vals, pos, m)
+        cand = sorted(pos.tolist())  # pool order -> positional tie-break inside k-center
+        mine = [p for p in cand if lo <= p < hi]
+        emb_c = D.gather_rows(_embed_positions(eng, psrc, mine))
+        emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
+        picks = eng.kcenter(torch.cat([emb_l, emb_c], 0), labeled_size, select_num, "l2")
+        return [pool.image_idx[cand[i - labeled_size]] for i in picks.tolist()]
+
+
+SELECTORS = {
+    "b200-entropy": B200EntropySelector,
+    "b200-margin": B200MarginSelector,
+    "b200-confidence": B200ConfidenceSelector,
+    "b200-mc-entropy": B200MCDropoutEntropySelector,
+    "b200-coreset-l2": lambda **kw: B200CoresetSelector(metric="l2", **kw),
+    "b200-coreset-cosine": lambda **kw: B200CoresetSelector(metric="cosine", **kw),
+    "b200-hybrid": B200HybridSelector,
+}

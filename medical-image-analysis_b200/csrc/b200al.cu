@@ -1,0 +1,889 @@
+// libb200al: C ABI + host-side plan for the acquisition pass (see include/b200al.h).
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -lineinfo -O3 -shared -Xcompiler -fPIC
+#include "../../include/b200al.h"
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "conv_tc.cuh"
+#include "kcenter.cuh"
+#include "topk.cuh"
+#include "uncertainty.cuh"
+#include "unet_misc.cuh"
+
+using namespace b200al;
+
+namespace {
+
+std::mutex g_err_mu;
+std::string g_last_error;
+
+constexpr int kChannels[5] = {32, 64, 128, 256, 512};
+
+// ---------------------------------------------------------------------------
+// activation buffers: NHWC, per pixel [hi plane (C_total) | lo plane (C_total)] bf16
+// ---------------------------------------------------------------------------
+enum BufId { E0A, CAT3, E1A, CAT2, E2A, CAT1, E3A, CAT0, E4A, E4B, D0A, D0B, D1A, D1B, D2A, D2B, D3A, D3B, NUM_BUFS };
+
+struct ActBuf {
+  __nv_bfloat16* ptr = nullptr;
+  int level = 0;    // resolution level: H >> level
+  int c_total = 0;  // channels per plane
+};
+
+struct ActView {  // a channel window of a buffer
+  int buf, c_off, c;
+};
+
+enum LayerKind { KIND_CONV3 = 0, KIND_CONVT = 1 };
+
+struct Layer {
+  int kind, cin, cout, stride;
+  ActView in, out;
+  int block = -1;  // PlainBlock index (mask offset source) or -1
+  int up = -1;     // upsample index or -1
+  int mask_off = 0;
+  int bn = 0, bk = 0, stages = 0;
+  __nv_bfloat16* wp = nullptr;  // packed weights [plane][tap][N][Cin]
+  float *scale = nullptr, *bias = nullptr, *shift = nullptr;
+  CUtensorMap tmA, tmB;
+  ConvTcParams p;
+  double flops_per_sample = 0;
+};
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+}  // namespace
+
+struct b200al_ctx {
+  int device = 0, K = 0, H = 0, W = 0, max_samples = 0, precision = 0;
+  int nsplit = 3;
+  bool weights_loaded = false;
+  std::string err;
+  EncodeTiledFn encode = nullptr;
+  ActBuf bufs[NUM_BUFS];
+  std::vector<Layer> layers;  // 21 tensor-core layers in forward order (first conv and head are separate)
+  // first conv + head
+  float *first_w = nullptr, *first_bias = nullptr, *first_scale = nullptr, *first_shift = nullptr;
+  float *head_w = nullptr, *head_b = nullptr;
+  float* ones = nullptr;   // [512] ones  (convT scale)
+  float* zeros = nullptr;  // [512] zeros (convT shift)
+  float* mask = nullptr;   // [max_samples][2944]
+  double* partial = nullptr;
+  int partial_blocks = 0;
+  float slope = 0.01f;
+  // k-center / top-k scratch
+  float *kc_part_val = nullptr, *kc_centre = nullptr;
+  int* kc_part_idx = nullptr;
+  int kc_blocks = 0;
+  unsigned long long *tk_keys = nullptr, *tk_cand = nullptr;
+  size_t tk_cap = 0;
+  TopkState* tk_state = nullptr;
+  // bookkeeping
+  long long launches = 0;
+  bool timing = false;
+  std::vector<cudaEvent_t> ev;
+  size_t ev_used = 0;
+  double conv_ms = 0, conv_flops = 0;
+  long long conv_launches = 0, conv_timed = 0;
+  std::vector<void*> allocs;
+  int sm_count = 148;
+};
+
+namespace {
+
+int set_err(b200al_ctx* ctx, int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  {
+    std::lock_guard<std::mutex> lk(g_err_mu);
+    g_last_error = buf;
+  }
+  if (ctx) ctx->err = buf;
+  return code;
+}
+
+#define CUDA_TRY(ctx, expr)                                                                        \
+  do {                                                                                             \
+    cudaError_t e__ = (expr);                                                                      \
+    if (e__ != cudaSuccess)                                                                        \
+      return set_err(ctx, B200AL_ERR_CUDA, "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e__), \
+                     __FILE__, __LINE__);                                                          \
+  } while (0)
+
+template <typename T>
+int dev_alloc(b200al_ctx* ctx, T** p, size_t count) {
+  void* q = nullptr;
+  CUDA_TRY(ctx, cudaMalloc(&q, count * sizeof(T)));
+  ctx->allocs.push_back(q);
+  *p = reinterpret_cast<T*>(q);
+  return 0;
+}
+
+int level_of(int buf) {
+  switch (buf) {
+    case E0A: case CAT3: case D3A: case D3B: return 0;
+    case E1A: case CAT2: case D2A: case D2B: return 1;
+    case E2A: case CAT1: case D1A: case D1B: return 2;
+    case E3A: case CAT0: case D0A: case D0B: return 3;
+    default: return 4;
+  }
+}
+int ctotal_of(int buf) {
+  switch (buf) {
+    case E0A: case D3A: case D3B: return 32;
+    case CAT3: case E1A: case D2A: case D2B: return 64;
+    case CAT2: case E2A: case D1A: case D1B: return 128;
+    case CAT1: case E3A: case D0A: case D0B: return 256;
+    case CAT0: case E4A: case E4B: return 512;
+  }
+  return 0;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// TMA descriptors
+// ---------------------------------------------------------------------------
+namespace {
+
+int load_encode_fn(b200al_ctx* ctx) {
+  void* fn = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  CUDA_TRY(ctx, cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres));
+  if (!fn || qres != cudaDriverEntryPointSuccess)
+    return set_err(ctx, B200AL_ERR_CUDA, "cuTensorMapEncodeTiled not available from the driver");
+  ctx->encode = reinterpret_cast<EncodeTiledFn>(fn);
+  return 0;
+}
+
+// A operand: activations [S, H, W, pitch] viewed 5-D.  stride 1: (pitch, W, 1, H, S);
+// stride 2: (2*pitch, W/2, 2, H/2, S) so that every filter tap is a dense box.
+int make_tma_act(b200al_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int S, int H, int W, int pitch,
+                 int stride, int bk, int tw, int th) {
+  cuuint64_t dims[5], strides[4];
+  const cuuint64_t pb = (cuuint64_t)pitch * 2;
+  if (stride == 1) {
+    dims[0] = pitch; dims[1] = W; dims[2] = 1; dims[3] = H; dims[4] = S;
+    strides[0] = pb; strides[1] = pb * W; strides[2] = pb * W; strides[3] = pb * W * H;
+  } else {
+    dims[0] = 2 * pitch; dims[1] = W / 2; dims[2] = 2; dims[3] = H / 2; dims[4] = S;
+    strides[0] = 2 * pb; strides[1] = pb * W; strides[2] = 2 * pb * W; strides[3] = pb * W * H;
+  }
+  cuuint32_t box[5] = {(cuuint32_t)bk, (cuuint32_t)tw, 1, (cuuint32_t)th, 1};
+  cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<__nv_bfloat16*>(base), dims, strides,
+                           box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_err(ctx, B200AL_ERR_CUDA, "cuTensorMapEncodeTiled(act) failed: %d", (int)r);
+  return 0;
+}
+
+// B operand: packed weights [rows = planes*taps*N][Cin], K-major.
+int make_tma_wgt(b200al_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int rows, int cin, int bk, int bn) {
+  cuuint64_t dims[2] = {(cuuint64_t)cin, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cin * 2};
+  cuuint32_t box[2] = {(cuuint32_t)bk, (cuuint32_t)bn};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<__nv_bfloat16*>(base), dims, strides,
+                           box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                           bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
+                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return set_err(ctx, B200AL_ERR_CUDA, "cuTensorMapEncodeTiled(wgt) failed: %d", (int)r);
+  return 0;
+}
+
+// ---------------------------------------------------------------------------
+// tcgen05 conv dispatch
+// ---------------------------------------------------------------------------
+typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const ConvTcParams, const int);
+
+template <int BN, int BK>
+ConvKernelFn pick_split(int nsplit) {
+  return nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<BN, BK, 3> : (ConvKernelFn)conv_tc_kernel<BN, BK, 1>;
+}
+ConvKernelFn pick_kernel(int bn, int bk, int nsplit) {
+  if (bk == 32) {
+    if (bn == 32) return pick_split<32, 32>(nsplit);
+    if (bn == 64) return pick_split<64, 32>(nsplit);
+    return nullptr;
+  }
+  switch (bn) {
+    case 32: return pick_split<32, 64>(nsplit);
+    case 64: return pick_split<64, 64>(nsplit);
+    case 128: return pick_split<128, 64>(nsplit);
+    case 256: return pick_split<256, 64>(nsplit);
+  }
+  return nullptr;
+}
+int stage_bytes(int bn, int bk, int nsplit) { return (nsplit == 3 ? 2 : 1) * (128 * bk * 2 + bn * bk * 2); }
+int conv_smem_bytes(int bn, int bk, int nsplit, int stages) {
+  return stages * stage_bytes(bn, bk, nsplit) + 1024 + 2 * bn * 4 + 1024;
+}
+
+int env_int(const char* name, int dflt) {
+  const char* v = getenv(name);
+  return v ? atoi(v) : dflt;
+}
+
+void choose_tile(int W, int* tw, int* th) {
+  *tw = W >= 16 ? 16 : W;
+  *th = 128 / *tw;
+}
+
+// Fill the parts of a layer's plan that depend only on shapes.
+int plan_layer(b200al_ctx* ctx, Layer& L) {
+  const ActBuf& ib = ctx->bufs[L.in.buf];
+  const ActBuf& ob = ctx->bufs[L.out.buf];
+  const int inH = ctx->H >> ib.level, inW = ctx->W >> ib.level;
+  const int outH = ctx->H >> ob.level, outW = ctx->W >> ob.level;
+  const int in_pitch = 2 * ib.c_total, out_pitch = 2 * ob.c_total;
+  ConvTcParams& p = L.p;
+  memset(&p, 0, sizeof(p));
+  L.bk = (L.cin % 64 == 0) ? 64 : 32;
+  const int n_total = L.kind == KIND_CONVT ? 4 * L.cout : L.cout;
+  const int bn_max = env_int("B200AL_BN_MAX", 128);
+  L.bn = n_total < bn_max ? n_total : bn_max;
+  if (L.kind == KIND_CONVT && L.bn > L.cout && (L.bn % L.cout) != 0) L.bn = L.cout;
+  if (L.bk == 32 && L.bn > 64) L.bn = 64;
+  const int sb = stage_bytes(L.bn, L.bk, ctx->nsplit);
+  const int budget = env_int("B200AL_SMEM_BUDGET", 98304);
+  int st = budget / sb;
+  if (st < 2) st = (200 * 1024) / sb;
+  if (st > 8) st = 8;
+  if (st < 2) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "conv tile does not fit shared memory");
+  L.stages = st;
+  p.taps = L.kind == KIND_CONV3 ? 9 : 1;
+  p.chunks = L.cin / L.bk;
+  p.n_total = n_total;
+  p.a_lo_off = ib.c_total;
+  const int gridW = L.kind == KIND_CONV3 ? outW : inW, gridH = L.kind == KIND_CONV3 ? outH : inH;
+  choose_tile(gridW, &p.tw, &p.th);
+  if (gridW % p.tw || gridH % p.th)
+    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "image size %dx%d not tileable at level %d", ctx->H, ctx->W, ob.level);
+  p.tiles_x = gridW / p.tw;
+  p.tiles_y = gridH / p.th;
+  for (int i = 0; i < 3; ++i) {
+    if (L.kind == KIND_CONVT) {
+      p.a_c0[i] = L.in.c_off; p.a_dx[i] = 0; p.a_p[i] = 0; p.a_dy[i] = 0;
+    } else if (L.stride == 1) {
+      p.a_c0[i] = L.in.c_off; p.a_dx[i] = i - 1; p.a_p[i] = 0; p.a_dy[i] = i - 1;
+    } else {
+      // input pixel 2*o + i - 1: i=0 -> (o-1, parity 1); i=1 -> (o, 0); i=2 -> (o, 1)
+      const int par = (i == 1) ? 0 : 1;
+      p.a_c0[i] = par * in_pitch + L.in.c_off;
+      p.a_dx[i] = (i == 0) ? -1 : 0;
+      p.a_p[i] = par;
+      p.a_dy[i] = (i == 0) ? -1 : 0;
+    }
+  }
+  p.slope = L.kind == KIND_CONV3 ? ctx->slope : 1.0f;
+  p.out = ob.ptr;
+  p.out_pitch = out_pitch;
+  p.out_hi_off = L.out.c_off;
+  p.out_lo_off = ob.c_total + L.out.c_off;
+  p.out_W = outW;
+  p.out_H = outH;
+  p.shuffle = L.kind == KIND_CONVT;
+  p.cout = L.cout;
+  p.write_lo = ctx->nsplit == 3;
+  p.mask_stride = B200AL_MASK_CHANNELS;
+  const double px = L.kind == KIND_CONV3 ? (double)outH * outW : (double)inH * inW;
+  L.flops_per_sample = 2.0 * px * n_total * (double)(p.taps * L.cin);
+  return 0;
+}
+
+int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const ConvTcParams& p, int S, cudaStream_t st) {
+  ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit);
+  if (!fn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no conv kernel for BN=%d BK=%d", L.bn, L.bk);
+  dim3 grid((unsigned)(S * p.tiles_x * p.tiles_y), (unsigned)(p.n_total / L.bn));
+  const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages);
+  const bool t = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
+  if (t) { cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
+  fn<<<grid, kConvThreads, smem, st>>>(tmA, L.tmB, p, L.stages);
+  if (t) cudaEventRecord(ctx->ev[ctx->ev_used++], st);
+  ctx->launches++;
+  ctx->conv_launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return 0;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------
+// context
+// ---------------------------------------------------------------------------
+namespace {
+
+void add_conv(b200al_ctx* ctx, int block, int cin, int cout, int stride, ActView in, ActView out, int mask_off) {
+  Layer L;
+  L.kind = KIND_CONV3; L.cin = cin; L.cout = cout; L.stride = stride; L.in = in; L.out = out;
+  L.block = block; L.mask_off = mask_off;
+  ctx->layers.push_back(L);
+}
+void add_convT(b200al_ctx* ctx, int up, int cin, int cout, ActView in, ActView out) {
+  Layer L;
+  L.kind = KIND_CONVT; L.cin = cin; L.cout = cout; L.stride = 1; L.in = in; L.out = out; L.up = up;
+  ctx->layers.push_back(L);
+}
+
+// mask channel offset of PlainBlock b (forward order; sum = 2944)
+int mask_offset(int b) {
+  static const int c[18] = {32, 32, 64, 64, 128, 128, 256, 256, 512, 512, 256, 256, 128, 128, 64, 64, 32, 32};
+  int off = 0;
+  for (int i = 0; i < b; ++i) off += c[i];
+  return off;
+}
+
+void build_layer_list(b200al_ctx* ctx) {
+  // encoder (unet.py:53-78): block 0 (first conv) is handled by conv_first_kernel
+  add_conv(ctx, 1, 32, 32, 1, {E0A, 0, 32}, {CAT3, 0, 32}, mask_offset(1));
+  add_conv(ctx, 2, 32, 64, 2, {CAT3, 0, 32}, {E1A, 0, 64}, mask_offset(2));
+  add_conv(ctx, 3, 64, 64, 1, {E1A, 0, 64}, {CAT2, 0, 64}, mask_offset(3));
+  add_conv(ctx, 4, 64, 128, 2, {CAT2, 0, 64}, {E2A, 0, 128}, mask_offset(4));
+  add_conv(ctx, 5, 128, 128, 1, {E2A, 0, 128}, {CAT1, 0, 128}, mask_offset(5));
+  add_conv(ctx, 6, 128, 256, 2, {CAT1, 0, 128}, {E3A, 0, 256}, mask_offset(6));
+  add_conv(ctx, 7, 256, 256, 1, {E3A, 0, 256}, {CAT0, 0, 256}, mask_offset(7));
+  add_conv(ctx, 8, 256, 512, 2, {CAT0, 0, 256}, {E4A, 0, 512}, mask_offset(8));
+  add_conv(ctx, 9, 512, 512, 1, {E4A, 0, 512}, {E4B, 0, 512}, mask_offset(9));
+  // decoder (unet.py:208-224): upsample -> cat([skip, up]) -> two blocks
+  add_convT(ctx, 0, 512, 256, {E4B, 0, 512}, {CAT0, 256, 256});
+  add_conv(ctx, 10, 512, 256, 1, {CAT0, 0, 512}, {D0A, 0, 256}, mask_offset(10));
+  add_conv(ctx, 11, 256, 256, 1, {D0A, 0, 256}, {D0B, 0, 256}, mask_offset(11));
+  add_convT(ctx, 1, 256, 128, {D0B, 0, 256}, {CAT1, 128, 128});
+  add_conv(ctx, 12, 256, 128, 1, {CAT1, 0, 256}, {D1A, 0, 128}, mask_offset(12));
+  add_conv(ctx, 13, 128, 128, 1, {D1A, 0, 128}, {D1B, 0, 128}, mask_offset(13));
+  add_convT(ctx, 2, 128, 64, {D1B, 0, 128}, {CAT2, 64, 64});
+  add_conv(ctx, 14, 128, 64, 1, {CAT2, 0, 128}, {D2A, 0, 64}, mask_offset(14));
+  add_conv(ctx, 15, 64, 64, 1, {D2A, 0, 64}, {D2B, 0, 64}, mask_offset(15));
+  add_convT(ctx, 3, 64, 32, {D2B, 0, 64}, {CAT3, 32, 32});
+  add_conv(ctx, 16, 64, 32, 1, {CAT3, 0, 64}, {D3A, 0, 32}, mask_offset(16));
+  add_conv(ctx, 17, 32, 32, 1, {D3A, 0, 32}, {D3B, 0, 32}, mask_offset(17));
+}
+
+constexpr int kEncoderLayers = 9;  // layers[0..8] end at the bottleneck (E4B)
+
+}  // namespace
+
+extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int in_channels, int H, int W,
+                                 int max_samples, int precision) {
+  if (!out) return set_err(nullptr, B200AL_ERR_ARG, "out is NULL");
+  *out = nullptr;
+  if (in_channels != 1)
+    return set_err(nullptr, B200AL_ERR_UNSUPPORTED, "in_channels=%d: only grayscale input (1) is supported", in_channels);
+  if (num_out < 2 || num_out > kMaxClasses)
+    return set_err(nullptr, B200AL_ERR_UNSUPPORTED, "num_out=%d outside [2,%d]", num_out, kMaxClasses);
+  if (H < 128 || W < 256 || H % 128 || W % 256)
+    return set_err(nullptr, B200AL_ERR_UNSUPPORTED, "H must be a multiple of 128 and W of 256 (got %dx%d)", H, W);
+  if (max_samples < 1) return set_err(nullptr, B200AL_ERR_ARG, "max_samples must be >= 1");
+  if (precision != B200AL_BF16X3 && precision != B200AL_BF16) return set_err(nullptr, B200AL_ERR_ARG, "bad precision");
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
+    return set_err(nullptr, B200AL_ERR_CUDA, "no CUDA device visible: libb200al has no CPU fallback");
+  if (device < 0 || device >= ndev) return set_err(nullptr, B200AL_ERR_ARG, "device %d out of range", device);
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess || prop.major != 10)
+    return set_err(nullptr, B200AL_ERR_CUDA, "device %d is not sm_100 (compute capability %d.%d)", device, prop.major,
+                   prop.minor);
+  b200al_ctx* ctx = new b200al_ctx();
+  ctx->device = device; ctx->K = num_out; ctx->H = H; ctx->W = W; ctx->max_samples = max_samples;
+  ctx->precision = precision; ctx->nsplit = precision == B200AL_BF16X3 ? 3 : 1;
+  ctx->sm_count = prop.multiProcessorCount;
+  int rc = 0;
+#define TRY_RC(x) do { rc = (x); if (rc) { g_last_error = ctx->err; b200al_ctx_destroy(ctx); return rc; } } while (0)
+#define TRY_CU(x) do { cudaError_t e__ = (x); if (e__ != cudaSuccess) { rc = set_err(ctx, B200AL_ERR_CUDA, "%s: %s", #x, cudaGetErrorString(e__)); b200al_ctx_destroy(ctx); return rc; } } while (0)
+  TRY_CU(cudaSetDevice(device));
+  TRY_RC(load_encode_fn(ctx));
+  for (int b = 0; b < NUM_BUFS; ++b) {
+    ctx->bufs[b].level = level_of(b);
+    ctx->bufs[b].c_total = ctotal_of(b);
+    const size_t elems = (size_t)max_samples * (H >> level_of(b)) * (W >> level_of(b)) * 2 * ctotal_of(b);
+    TRY_RC(dev_alloc(ctx, &ctx->bufs[b].ptr, elems));
+  }
+  build_layer_list(ctx);
+  for (Layer& L : ctx->layers) {
+    TRY_RC(plan_layer(ctx, L));
+    const int taps = L.kind == KIND_CONV3 ? 9 : 4;
+    TRY_RC(dev_alloc(ctx, &L.wp, (size_t)2 * taps * L.cout * L.cin));
+    TRY_RC(dev_alloc(ctx, &L.scale, (size_t)L.cout));
+    TRY_RC(dev_alloc(ctx, &L.bias, (size_t)L.cout));
+    TRY_RC(dev_alloc(ctx, &L.shift, (size_t)L.cout));
+    const ActBuf& ib = ctx->bufs[L.in.buf];
+    TRY_RC(make_tma_act(ctx, &L.tmA, ib.ptr, max_samples, H >> ib.level, W >> ib.level, 2 * ib.c_total,
+                        L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw, L.p.th));
+    // rows: conv [2 planes][9 taps][Cout]; convT [2 planes][1][4*Cout]
+    TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn));
+    ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit);
+    if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d", L.bn, L.bk); b200al_ctx_destroy(ctx); return rc; }
+    TRY_CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages)));
+  }
+  TRY_RC(dev_alloc(ctx, &ctx->first_w, 32 * 9));
+  TRY_RC(dev_alloc(ctx, &ctx->first_bias, 32));
+  TRY_RC(dev_alloc(ctx, &ctx->first_scale, 32));
+  TRY_RC(dev_alloc(ctx, &ctx->first_shift, 32));
+  TRY_RC(dev_alloc(ctx, &ctx->head_w, (size_t)kMaxClasses * 32));
+  TRY_RC(dev_alloc(ctx, &ctx->head_b, (size_t)kMaxClasses));
+  TRY_RC(dev_alloc(ctx, &ctx->ones, 512));
+  TRY_RC(dev_alloc(ctx, &ctx->zeros, 512));
+  TRY_RC(dev_alloc(ctx, &ctx->mask, (size_t)max_samples * B200AL_MASK_CHANNELS));
+  ctx->partial_blocks = 64;
+  TRY_RC(dev_alloc(ctx, &ctx->partial, (size_t)max_samples * ctx->partial_blocks));
+  ctx->kc_blocks = ctx->sm_count * 4;
+  TRY_RC(dev_alloc(ctx, &ctx->kc_part_val, (size_t)ctx->kc_blocks));
+  TRY_RC(dev_alloc(ctx, &ctx->kc_part_idx, (size_t)ctx->kc_blocks));
+  TRY_RC(dev_alloc(ctx, &ctx->kc_centre, 1024));
+  TRY_RC(dev_alloc(ctx, &ctx->tk_state, 1));
+  fill_kernel<<<2, 256>>>(ctx->ones, 1.0f, 512);
+  fill_kernel<<<2, 256>>>(ctx->zeros, 0.0f, 512);
+  TRY_CU(cudaDeviceSynchronize());
+  ctx->ev.resize(2 * 32768);
+  for (auto& e : ctx->ev) TRY_CU(cudaEventCreate(&e));
+#undef TRY_RC
+#undef TRY_CU
+  *out = ctx;
+  return B200AL_OK;
+}
+
+extern "C" void b200al_ctx_destroy(b200al_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  for (void* p : ctx->allocs) cudaFree(p);
+  if (ctx->tk_keys) cudaFree(ctx->tk_keys);
+  if (ctx->tk_cand) cudaFree(ctx->tk_cand);
+  for (auto& e : ctx->ev)
+    if (e) cudaEventDestroy(e);
+  delete ctx;
+}
+
+extern "C" const char* b200al_last_error(const b200al_ctx* ctx) {
+  if (ctx) return ctx->err.c_str();
+  static thread_local std::string copy;
+  std::lock_guard<std::mutex> lk(g_err_mu);
+  copy = g_last_error;
+  return copy.c_str();
+}
+
+// ---------------------------------------------------------------------------
+// weights
+// ---------------------------------------------------------------------------
+extern "C" int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, void* stream) {
+  if (!ctx || !w) return set_err(ctx, B200AL_ERR_ARG, "NULL argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  ctx->slope = w->leaky_slope;
+  const b200al_block_weights& b0 = w->blocks[0];
+  if (!b0.d_conv_weight || !w->d_head_weight || !w->d_head_bias) return set_err(ctx, B200AL_ERR_ARG, "NULL weight pointer");
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->first_w, b0.d_conv_weight, 32 * 9 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->first_bias, b0.d_conv_bias, 32 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  fold_bn_kernel<<<1, 32, 0, st>>>(b0.d_bn_gamma, b0.d_bn_beta, b0.d_bn_mean, b0.d_bn_var, w->bn_eps, ctx->first_scale,
+                                   ctx->first_shift, 32);
+  for (Layer& L : ctx->layers) {
+    L.p.slope = L.kind == KIND_CONV3 ? ctx->slope : 1.0f;
+    if (L.kind == KIND_CONV3) {
+      const b200al_block_weights& b = w->blocks[L.block];
+      if (!b.d_conv_weight || !b.d_conv_bias || !b.d_bn_gamma || !b.d_bn_beta || !b.d_bn_mean || !b.d_bn_var)
+        return set_err(ctx, B200AL_ERR_ARG, "NULL weight pointer in block %d", L.block);
+      pack_conv3x3_kernel<<<256, 256, 0, st>>>(b.d_conv_weight, L.wp, L.cout, L.cin);
+      CUDA_TRY(ctx, cudaMemcpyAsync(L.bias, b.d_conv_bias, L.cout * sizeof(float), cudaMemcpyDeviceToDevice, st));
+      fold_bn_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(b.d_bn_gamma, b.d_bn_beta, b.d_bn_mean, b.d_bn_var,
+                                                          w->bn_eps, L.scale, L.shift, L.cout);
+    } else {
+      if (!w->d_up_weight[L.up] || !w->d_up_bias[L.up]) return set_err(ctx, B200AL_ERR_ARG, "NULL upsample weight %d", L.up);
+      pack_convT_kernel<<<256, 256, 0, st>>>(w->d_up_weight[L.up], L.wp, L.cin, L.cout);
+      CUDA_TRY(ctx, cudaMemcpyAsync(L.bias, w->d_up_bias[L.up], L.cout * sizeof(float), cudaMemcpyDeviceToDevice, st));
+      CUDA_TRY(ctx, cudaMemcpyAsync(L.scale, ctx->ones, L.cout * sizeof(float), cudaMemcpyDeviceToDevice, st));
+      CUDA_TRY(ctx, cudaMemcpyAsync(L.shift, ctx->zeros, L.cout * sizeof(float), cudaMemcpyDeviceToDevice, st));
+    }
+    L.p.scale = L.scale; L.p.bias = L.bias; L.p.shift = L.shift;
+    ctx->launches += 2;
+  }
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->head_w, w->d_head_weight, (size_t)ctx->K * 32 * sizeof(float),
+                                cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->head_b, w->d_head_bias, (size_t)ctx->K * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  CUDA_TRY(ctx, cudaGetLastError());
+  ctx->weights_loaded = true;
+  return B200AL_OK;
+}
+
+// ---------------------------------------------------------------------------
+// forward
+// ---------------------------------------------------------------------------
+namespace {
+
+int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, int S, int T, const float* mask, cudaStream_t st) {
+  dim3 grid((ctx->W + 255) / 256, ctx->H, S);
+  const ActBuf& ob = ctx->bufs[E0A];
+  if (dtype == B200AL_U8)
+    conv_first_kernel<uint8_t><<<grid, 256, 0, st>>>((const uint8_t*)d_images, T, ctx->H, ctx->W, ctx->first_w,
+                                                    ctx->first_bias, ctx->first_scale, ctx->first_shift, mask,
+                                                    B200AL_MASK_CHANNELS, ctx->slope, ob.ptr, 2 * ob.c_total, 0,
+                                                    ob.c_total, ctx->nsplit == 3);
+  else if (dtype == B200AL_F32)
+    conv_first_kernel<float><<<grid, 256, 0, st>>>((const float*)d_images, T, ctx->H, ctx->W, ctx->first_w,
+                                                  ctx->first_bias, ctx->first_scale, ctx->first_shift, mask,
+                                                  B200AL_MASK_CHANNELS, ctx->slope, ob.ptr, 2 * ob.c_total, 0,
+                                                  ob.c_total, ctx->nsplit == 3);
+  else
+    return set_err(ctx, B200AL_ERR_ARG, "bad image dtype %d", dtype);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return 0;
+}
+
+// layers [0, n_layers) of ctx->layers on S samples; mask nullable [S][2944]
+int run_layers(b200al_ctx* ctx, int n_layers, int S, const float* mask, cudaStream_t st) {
+  for (int i = 0; i < n_layers; ++i) {
+    Layer& L = ctx->layers[i];
+    ConvTcParams p = L.p;
+    p.mask = (mask && L.kind == KIND_CONV3) ? mask + L.mask_off : nullptr;
+    int rc = launch_conv(ctx, L, L.tmA, p, S, st);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+int prepare_masks(b200al_ctx* ctx, int n, int T, float drop_p, uint64_t seed, int64_t base_pos,
+                  const float* d_user_masks, const float** mask_out, cudaStream_t st) {
+  *mask_out = nullptr;
+  if (d_user_masks) { *mask_out = d_user_masks; return 0; }
+  if (drop_p <= 0.f) return 0;
+  if (drop_p >= 1.f) return set_err(ctx, B200AL_ERR_ARG, "drop_p must be < 1");
+  const uint32_t thr = (uint32_t)floor((double)drop_p * 16777216.0);
+  const float keep_scale = 1.0f / (1.0f - drop_p);
+  const long long total = (long long)n * T * B200AL_MASK_CHANNELS;
+  const int blocks = (int)((total + 255) / 256 < 4096 ? (total + 255) / 256 : 4096);
+  mc_mask_kernel<<<blocks, 256, 0, st>>>(ctx->mask, n * T, T, B200AL_MASK_CHANNELS, seed, (long long)base_pos, thr,
+                                        keep_scale);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  *mask_out = ctx->mask;
+  return 0;
+}
+
+template <int K>
+void launch_head(b200al_ctx* ctx, int n, int T, int mode, float smooth, float* logits, cudaStream_t st) {
+  const ActBuf& fb = ctx->bufs[D3B];
+  dim3 grid(ctx->partial_blocks, n);
+  head_uncertainty_kernel<K><<<grid, 256, 0, st>>>(fb.ptr, 2 * fb.c_total, 0, fb.c_total, ctx->nsplit == 3,
+                                                  ctx->H * ctx->W, T, ctx->head_w, ctx->head_b, mode, smooth, logits,
+                                                  ctx->partial);
+}
+
+template <int K>
+void launch_unc(const float* logits, int n, int T, int HW, int mode, float smooth, double* partial, int nblk,
+                cudaStream_t st) {
+  dim3 grid(nblk, n);
+  uncertainty_logits_kernel<K><<<grid, 256, 0, st>>>(logits, T, HW, mode, smooth, partial);
+}
+
+#define DISPATCH_K(K_, CALL)                         \
+  switch (K_) {                                      \
+    case 2: CALL(2); break;                          \
+    case 3: CALL(3); break;                          \
+    case 4: CALL(4); break;                          \
+    case 5: CALL(5); break;                          \
+    case 6: CALL(6); break;                          \
+    case 7: CALL(7); break;                          \
+    case 8: CALL(8); break;                          \
+    default: break;                                  \
+  }
+
+}  // namespace
+
+extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int image_dtype, int n, int mode, int T,
+                                  float drop_p, uint64_t mc_seed, int64_t base_pos, const float* d_drop_masks,
+                                  float smooth, float* d_scores_out, float* d_logits_out, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (!ctx->weights_loaded) return set_err(ctx, B200AL_ERR_STATE, "b200al_load_weights has not been called");
+  if (n == 0) return B200AL_OK;
+  if (!d_images || !d_scores_out || n < 0 || T < 1) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if ((long long)n * T > ctx->max_samples)
+    return set_err(ctx, B200AL_ERR_ARG, "n*T = %lld exceeds max_samples = %d", (long long)n * T, ctx->max_samples);
+  if (mode < 0 || mode > 2) return set_err(ctx, B200AL_ERR_ARG, "bad score mode %d", mode);
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const float* mask = nullptr;
+  int rc = prepare_masks(ctx, n, T, drop_p, mc_seed, base_pos, d_drop_masks, &mask, st);
+  if (rc) return rc;
+  const int S = n * T;
+  if ((rc = run_first_conv(ctx, d_images, image_dtype, S, T, mask, st))) return rc;
+  if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st))) return rc;
+#define CALL_HEAD(KK) launch_head<KK>(ctx, n, T, mode, smooth, d_logits_out, st)
+  DISPATCH_K(ctx->K, CALL_HEAD)
+#undef CALL_HEAD
+  uncertainty_finalize_kernel<<<(n + 127) / 128, 128, 0, st>>>(ctx->partial, ctx->partial_blocks, ctx->H * ctx->W,
+                                                              d_scores_out, n);
+  ctx->launches += 2;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+extern "C" int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, int n, float* d_emb_out,
+                                 void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (!ctx->weights_loaded) return set_err(ctx, B200AL_ERR_STATE, "b200al_load_weights has not been called");
+  if (n == 0) return B200AL_OK;
+  if (!d_images || !d_emb_out || n < 0) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (n > ctx->max_samples) return set_err(ctx, B200AL_ERR_ARG, "n = %d exceeds max_samples = %d", n, ctx->max_samples);
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int rc;
+  if ((rc = run_first_conv(ctx, d_images, image_dtype, n, 1, nullptr, st))) return rc;
+  if ((rc = run_layers(ctx, kEncoderLayers, n, nullptr, st))) return rc;
+  const ActBuf& bb = ctx->bufs[E4B];
+  avgpool_kernel<<<n, 512, 0, st>>>(bb.ptr, (ctx->H >> 4) * (ctx->W >> 4), 2 * bb.c_total, 0, bb.c_total,
+                                    ctx->nsplit == 3, bb.c_total, d_emb_out);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+extern "C" int b200al_uncertainty_from_logits(b200al_ctx* ctx, const float* d_logits, int n, int T, int K, int HW,
+                                              int mode, float smooth, float* d_scores_out, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (n == 0) return B200AL_OK;
+  if (!d_logits || !d_scores_out || n < 0 || T < 1 || K < 2 || K > kMaxClasses || HW < 4 || HW % 4)
+    return set_err(ctx, B200AL_ERR_ARG, "bad argument (need 2 <= K <= %d, HW %% 4 == 0)", kMaxClasses);
+  if (mode < 0 || mode > 2) return set_err(ctx, B200AL_ERR_ARG, "bad score mode %d", mode);
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int nblk = (HW / 4 + 255) / 256;
+  if (nblk > ctx->partial_blocks) nblk = ctx->partial_blocks;
+  for (int i0 = 0; i0 < n; i0 += ctx->max_samples) {
+    const int nn = (n - i0) < ctx->max_samples ? (n - i0) : ctx->max_samples;
+    const float* lg = d_logits + (size_t)i0 * T * K * HW;
+#define CALL_UNC(KK) launch_unc<KK>(lg, nn, T, HW, mode, smooth, ctx->partial, nblk, st)
+    DISPATCH_K(K, CALL_UNC)
+#undef CALL_UNC
+    uncertainty_finalize_kernel<<<(nn + 127) / 128, 128, 0, st>>>(ctx->partial, nblk, HW, d_scores_out + i0, nn);
+    ctx->launches += 2;
+  }
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+// ---------------------------------------------------------------------------
+// rank & cut
+// ---------------------------------------------------------------------------
+extern "C" int b200al_topk(b200al_ctx* ctx, const float* d_scores, int n, int k, int64_t base_pos,
+                           float* d_out_scores, int64_t* d_out_pos, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (n < 0 || k < 0) return set_err(ctx, B200AL_ERR_ARG, "negative size");
+  if (k > n) k = n;
+  if (k == 0) return B200AL_OK;
+  if (!d_scores || !d_out_scores || !d_out_pos) return set_err(ctx, B200AL_ERR_ARG, "NULL pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if ((size_t)n > ctx->tk_cap) {
+    CUDA_TRY(ctx, cudaStreamSynchronize(st));
+    if (ctx->tk_keys) cudaFree(ctx->tk_keys);
+    if (ctx->tk_cand) cudaFree(ctx->tk_cand);
+    ctx->tk_keys = ctx->tk_cand = nullptr;
+    ctx->tk_cap = 0;
+    CUDA_TRY(ctx, cudaMalloc(&ctx->tk_keys, (size_t)n * sizeof(unsigned long long)));
+    CUDA_TRY(ctx, cudaMalloc(&ctx->tk_cand, (size_t)n * sizeof(unsigned long long)));
+    ctx->tk_cap = (size_t)n;
+  }
+  const int blocks = (n + 255) / 256 < ctx->sm_count * 8 ? (n + 255) / 256 : ctx->sm_count * 8;
+  topk_keys_kernel<<<blocks, 256, 0, st>>>(d_scores, n, ctx->tk_keys, ctx->tk_state, (unsigned)k);
+  for (int pass = 0; pass < 8; ++pass) {
+    topk_hist_kernel<<<blocks, 256, 0, st>>>(ctx->tk_keys, n, ctx->tk_state, pass);
+    topk_scan_kernel<<<1, 32, 0, st>>>(ctx->tk_state, pass);
+  }
+  topk_compact_kernel<<<blocks, 256, 0, st>>>(ctx->tk_keys, n, ctx->tk_state, ctx->tk_cand, (unsigned)k);
+  topk_rank_kernel<<<(k + 255) / 256, 256, 0, st>>>(ctx->tk_cand, (unsigned)k, (long long)base_pos, d_out_scores,
+                                                   (long long*)d_out_pos);
+  ctx->launches += 19;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+// ---------------------------------------------------------------------------
+// k-center greedy
+// ---------------------------------------------------------------------------
+namespace {
+template <int NV>
+void launch_kc_init(const float* emb, int n, const float* centres, int L, int metric, float* mind, int accumulate,
+                    int blocks, cudaStream_t st) {
+  kcenter_init_kernel<NV, (NV <= 4 ? 4 : 2)><<<blocks, 256, 0, st>>>(emb, n, centres, L, metric, mind, accumulate);
+}
+template <int NV>
+void launch_kc_step(const float* emb, int n, const float* centre, int do_update, int metric, float* mind,
+                    const uint8_t* taken, float* pv, int* pi, int blocks, cudaStream_t st) {
+  kcenter_step_kernel<NV><<<blocks, 256, 0, st>>>(emb, n, centre, do_update, metric, mind, taken, pv, pi);
+}
+int check_dim(b200al_ctx* ctx, int D) {
+  if (D != 128 && D != 256 && D != 512 && D != 1024)
+    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "embedding dim %d not in {128,256,512,1024}", D);
+  return 0;
+}
+}  // namespace
+
+extern "C" int b200al_normalize_rows(b200al_ctx* ctx, const float* d_in, float* d_out, int n, int D, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (n == 0) return B200AL_OK;
+  if (!d_in || !d_out || n < 0 || D < 1) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  normalize_rows_kernel<<<(n + 7) / 8, 256, 0, (cudaStream_t)stream>>>(d_in, d_out, n, D);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+extern "C" int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, int D, const float* d_centres, int L,
+                                   int metric, float* d_mind, int accumulate, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (n == 0) return B200AL_OK;
+  if (!d_emb || !d_centres || !d_mind || n < 0) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (L < 1) return set_err(ctx, B200AL_ERR_ARG, "k-center needs at least one initial centre (L >= 1)");
+  if (metric != B200AL_L2 && metric != B200AL_COSINE) return set_err(ctx, B200AL_ERR_ARG, "bad metric");
+  if (int rc = check_dim(ctx, D)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int blocks = (n + 31) / 32;  // 8 warps x 4 rows
+  if (blocks > ctx->sm_count * 8) blocks = ctx->sm_count * 8;
+  switch (D / 128) {
+    case 1: launch_kc_init<1>(d_emb, n, d_centres, L, metric, d_mind, accumulate, blocks, st); break;
+    case 2: launch_kc_init<2>(d_emb, n, d_centres, L, metric, d_mind, accumulate, blocks, st); break;
+    case 4: launch_kc_init<4>(d_emb, n, d_centres, L, metric, d_mind, accumulate, blocks, st); break;
+    case 8: launch_kc_init<8>(d_emb, n, d_centres, L, metric, d_mind, accumulate, blocks, st); break;
+  }
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+extern "C" int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, float* d_mind,
+                                  uint8_t* d_taken, int budget, int64_t* d_picks, float* d_pick_vals, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (budget == 0) return B200AL_OK;
+  if (!d_emb || !d_mind || !d_taken || !d_picks || n < 1 || budget < 0) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (metric != B200AL_L2 && metric != B200AL_COSINE) return set_err(ctx, B200AL_ERR_ARG, "bad metric");
+  if (int rc = check_dim(ctx, D)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int blocks = (n + 63) / 64;  // >= 8 rows per warp
+  if (blocks > ctx->kc_blocks) blocks = ctx->kc_blocks;
+  if (blocks < 1) blocks = 1;
+  for (int step = 0; step < budget; ++step) {
+    const int upd = step > 0;
+    switch (D / 128) {
+      case 1: launch_kc_step<1>(d_emb, n, ctx->kc_centre, upd, metric, d_mind, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 2: launch_kc_step<2>(d_emb, n, ctx->kc_centre, upd, metric, d_mind, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 4: launch_kc_step<4>(d_emb, n, ctx->kc_centre, upd, metric, d_mind, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 8: launch_kc_step<8>(d_emb, n, ctx->kc_centre, upd, metric, d_mind, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+    }
+    kcenter_pick_kernel<<<1, 256, 0, st>>>(ctx->kc_part_val, ctx->kc_part_idx, blocks, d_emb, D, d_taken,
+                                          ctx->kc_centre, (long long*)d_picks, d_pick_vals, step);
+    ctx->launches += 2;
+  }
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+// ---------------------------------------------------------------------------
+// introspection / timing
+// ---------------------------------------------------------------------------
+extern "C" int b200al_kernel_launches(const b200al_ctx* ctx, int64_t* out_count) {
+  if (!ctx || !out_count) return B200AL_ERR_ARG;
+  *out_count = ctx->launches;
+  return B200AL_OK;
+}
+
+extern "C" int b200al_set_timing(b200al_ctx* ctx, int enable) {
+  if (!ctx) return B200AL_ERR_ARG;
+  ctx->timing = enable != 0;
+  ctx->ev_used = 0;
+  ctx->conv_ms = 0;
+  ctx->conv_flops = 0;
+  ctx->conv_launches = 0;
+  ctx->conv_timed = 0;
+  return B200AL_OK;
+}
+
+// Synchronises the device, folds recorded event pairs into the running total.
+extern "C" int b200al_conv_time_ms(b200al_ctx* ctx, float* out_ms, int64_t* out_launches, double* out_flops) {
+  if (!ctx || !out_ms) return B200AL_ERR_ARG;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaDeviceSynchronize());
+  for (size_t i = 0; i + 1 < ctx->ev_used; i += 2) {
+    float ms = 0.f;
+    CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]));
+    ctx->conv_ms += ms;
+  }
+  ctx->ev_used = 0;
+  *out_ms = (float)ctx->conv_ms;
+  if (out_launches) *out_launches = ctx->conv_timed;
+  if (out_flops) *out_flops = ctx->conv_flops;
+  return B200AL_OK;
+}
+
+// ---------------------------------------------------------------------------
+// test hooks
+// ---------------------------------------------------------------------------
+// info: kind, cin, cout, stride, inH, inW, in_pitch, in_c_off, outH, outW, out_pitch, out_c_off
+extern "C" int b200al_debug_layer_info(b200al_ctx* ctx, int layer_index, int* info) {
+  if (!ctx || !info || layer_index < 0 || layer_index >= (int)ctx->layers.size()) return B200AL_ERR_ARG;
+  const Layer& L = ctx->layers[layer_index];
+  const ActBuf& ib = ctx->bufs[L.in.buf];
+  const ActBuf& ob = ctx->bufs[L.out.buf];
+  info[0] = L.kind; info[1] = L.cin; info[2] = L.cout; info[3] = L.stride;
+  info[4] = ctx->H >> ib.level; info[5] = ctx->W >> ib.level; info[6] = 2 * ib.c_total; info[7] = L.in.c_off;
+  info[8] = ctx->H >> ob.level; info[9] = ctx->W >> ob.level; info[10] = 2 * ob.c_total; info[11] = L.out.c_off;
+  return B200AL_OK;
+}
+
+extern "C" int b200al_debug_layer(b200al_ctx* ctx, int layer_index, int impl, const void* d_in, void* d_out,
+                                  int n_samples, const float* d_mask, void* stream) {
+  if (!ctx || !d_in || !d_out || layer_index < 0 || layer_index >= (int)ctx->layers.size())
+    return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (!ctx->weights_loaded) return set_err(ctx, B200AL_ERR_STATE, "weights not loaded");
+  if (n_samples < 1 || n_samples > ctx->max_samples) return set_err(ctx, B200AL_ERR_ARG, "bad n_samples");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  Layer& L = ctx->layers[layer_index];
+  const ActBuf& ib = ctx->bufs[L.in.buf];
+  const ActBuf& ob = ctx->bufs[L.out.buf];
+  const int inH = ctx->H >> ib.level, inW = ctx->W >> ib.level;
+  const float* mask = (d_mask && L.kind == KIND_CONV3) ? d_mask + L.mask_off : nullptr;
+  if (impl == 0) {
+    CUtensorMap tmA;
+    int rc = make_tma_act(ctx, &tmA, (const __nv_bfloat16*)d_in, n_samples, inH, inW, 2 * ib.c_total,
+                          L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw, L.p.th);
+    if (rc) return rc;
+    ConvTcParams p = L.p;
+    p.out = (__nv_bfloat16*)d_out;
+    p.mask = mask;
+    return launch_conv(ctx, L, tmA, p, n_samples, st);
+  }
+  ConvSimtParams q;
+  q.in = (const __nv_bfloat16*)d_in + L.in.c_off;
+  q.in_pitch = 2 * ib.c_total; q.in_lo_off = ib.c_total; q.in_H = inH; q.in_W = inW; q.cin = L.cin;
+  q.wp = L.wp; q.cout = L.cout; q.stride = L.stride; q.mode = L.kind == KIND_CONV3 ? 0 : 1;
+  q.use_lo = ctx->nsplit == 3;
+  q.scale = L.scale; q.bias = L.bias; q.shift = L.shift; q.mask = mask; q.mask_stride = B200AL_MASK_CHANNELS;
+  q.slope = L.p.slope;
+  q.out = (__nv_bfloat16*)d_out;
+  q.out_pitch = 2 * ob.c_total; q.out_hi_off = L.out.c_off; q.out_lo_off = ob.c_total + L.out.c_off;
+  q.out_H = ctx->H >> ob.level; q.out_W = ctx->W >> ob.level; q.write_lo = ctx->nsplit == 3;
+  conv_simt_kernel<<<ctx->sm_count * 16, 256, 0, st>>>(q, n_samples);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}

@@ -193,7 +193,7 @@ def conv_weight_digest(sd) -> str:
     return h.hexdigest()
 
 
-GOLDEN_BN_KEYS = (".2.weight", ".2.bias", ".2.running_mean", ".2.running_var")
+GOLDEN_BN_KEYS = (".all.2.weight", ".all.2.bias", ".all.2.running_mean", ".all.2.running_var")
 
 
 def build_calibrated_state_dict(num_out: int, images_u8: torch.Tensor, seed: int = 1337,
@@ -210,9 +210,9 @@ def build_calibrated_state_dict(num_out: int, images_u8: torch.Tensor, seed: int
     sd = make_state_dict(seed, num_out)
     g = torch.Generator().manual_seed(affine_seed)
     for k in sd:
-        if k.endswith(".2.weight"):
+        if k.endswith(".all.2.weight"):
             sd[k].copy_(0.5 + torch.rand(sd[k].shape, generator=g))
-        elif k.endswith(".2.bias"):
+        elif k.endswith(".all.2.bias"):
             sd[k].copy_(0.3 * torch.randn(sd[k].shape, generator=g))
     x = images_u8.to(torch.float32).div(255.0).unsqueeze(1)
     with torch.no_grad():

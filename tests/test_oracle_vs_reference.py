@@ -1,0 +1,106 @@
+"""Pins the oracle against the UNMODIFIED reference run here (container only;
+skipped on the GPU box where /root/reference does not exist)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle.ref_import import reference_available
+
+pytestmark = [pytest.mark.reference,
+              pytest.mark.skipif(not reference_available(), reason="/root/reference not present")]
+
+
+@pytest.fixture(scope="module")
+def ref():
+    from oracle.ref_import import load_reference
+    return load_reference()
+
+
+def test_seeded_weights_identical_to_reference_unet(ref):
+    from oracle.ref_import import build_reference_unet
+    from oracle.unet_ref import make_state_dict
+    torch.manual_seed(1337)
+    rsd = build_reference_unet(3).state_dict()
+    sd = make_state_dict(1337, 3)
+    assert list(rsd.keys()) == list(sd.keys())
+    assert all(torch.equal(rsd[k], sd[k]) for k in sd)
+
+
+def test_forward_and_embedding_identical(ref, golden):
+    from oracle.ref_import import build_reference_unet
+    from oracle.synth import synth_pool_u8
+    from oracle.unet_ref import golden_state_dict, unet_embed, unet_forward
+    sd = golden_state_dict(3, golden["model"])
+    m = build_reference_unet(3)
+    m.load_state_dict(sd)
+    m.eval()
+    x = synth_pool_u8(2, start=77).float().div(255).unsqueeze(1)
+    with torch.no_grad():
+        assert torch.equal(m(x), unet_forward(sd, x))
+        assert torch.equal(m.get_enc_feature(x), unet_embed(sd, x))
+
+
+def test_mc_masks_equal_dropout_modules_replaced(ref, golden):
+    """Composed MC oracle == reference module with each Dropout2d swapped for
+    an explicit-mask multiply."""
+    from oracle.ref_import import build_reference_unet
+    from oracle.synth import mc_masks, synth_pool_u8
+    from oracle.unet_ref import dropout_sites, golden_state_dict, unet_forward
+    sd = golden_state_dict(3, golden["model"])
+    m = build_reference_unet(3, dropout_prob=0.1)
+    m.load_state_dict(sd)
+    m.eval()
+    masks = mc_masks(11, [3], 1, 0.1)[:, 0]
+    sites, total = dropout_sites()
+    assert total == 2944
+
+    class Mul(torch.nn.Module):
+        def __init__(self, v):
+            super().__init__()
+            self.v = v
+
+        def forward(self, x):
+            return x * self.v[:, :, None, None]
+
+    for prefix, off, c in sites:
+        blk = m.get_submodule(prefix)
+        assert isinstance(blk[1], torch.nn.Dropout2d)
+        blk[1] = Mul(masks[:, off:off + c])
+    x = synth_pool_u8(1, start=3).float().div(255).unsqueeze(1)
+    with torch.no_grad():
+        np.testing.assert_allclose(m(x).numpy(), unet_forward(sd, x, masks=masks).numpy(), rtol=0, atol=1e-6)
+
+
+def test_kcenter_restatements_equal_reference(ref):
+    from sklearn.metrics import pairwise_distances
+    from oracle import select_ref as S
+    rng = np.random.default_rng(3)
+    for metric in ("l2", "cosine"):
+        feats = (rng.standard_normal((500, 512)) * 0.3 + 0.2).astype(np.float32)
+        dist = pairwise_distances(feats, metric=metric)
+        want = ref.kcenter_greedy(dist, 500, 40, np.arange(25), "min")
+        assert sorted(S.kcenter_greedy_matrix(dist, 40, np.arange(25))) == sorted(int(i) for i in want)
+        assert sorted(S.kcenter_greedy_stream(feats, 25, 40, metric)) == sorted(int(i) for i in want)
+        # the reference's /sum normalisation (coreset_selector.py:153) does not change the picks
+        d2 = dist / dist.sum()
+        assert sorted(int(i) for i in ref.kcenter_greedy(d2, 500, 40, np.arange(25), "min")) == sorted(int(i) for i in want)
+    col = S.l2_rows(feats, feats[7], 7)
+    np.testing.assert_array_equal(col, pairwise_distances(feats, metric="l2")[:, 7])
+
+
+def test_reference_selector_on_mirror_datasets(ref, golden):
+    """The reference's EntropySelector accepts the mirror dataset types the GPU
+    tests use, and returns the golden selection."""
+    from oracle.ref_import import build_reference_unet
+    from oracle.synth import make_active, synth_pool_u8
+    from oracle.unet_ref import golden_state_dict
+    g = golden["pool_K3"]
+    L, n = int(g["n_labeled"]), 6
+    sd = golden_state_dict(3, golden["model"])
+    m = build_reference_unet(3)
+    m.load_state_dict(sd)
+    ad = make_active(synth_pool_u8(L + n), L)
+    sel = ref.EntropySelector(batch_size=4, num_workers=0, pin_memory=False)
+    scores, names = sel.cal_scores(ad, m, torch.device("cpu"))
+    np.testing.assert_allclose(torch.stack(scores).numpy(), g["scores/entropy"][:n], rtol=1e-5)
+    assert names == ad.get_pool_dataset().image_idx
