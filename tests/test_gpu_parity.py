@@ -112,11 +112,14 @@ def test_coreset_selector_end_to_end(env, K, metric):
     ad = make_active(e["images"], e["L"])
     got = sel.select_next_batch(ad, e["k"], e["model"], torch.device(DEV))
     assert len(got) == e["k"] and len(set(got)) == e["k"]
+    if sorted(got) == e["g"][f"selected/coreset-{metric}"].tolist():
+        return
+    # A different set is acceptable only if the reference's own greedy run had a near-tie
+    # (top-2 gap below what a 1e-4 relative embedding error can move a distance by).
     _p, gaps = S.kcenter_greedy_stream(e["g"]["embeddings"], e["L"], e["k"], metric, return_gaps=True)
-    if min(gaps) > 1e-3 * np.abs(e["g"]["embeddings"]).max():   # greedy is stable against our embedding error
-        assert sorted(got) == e["g"][f"selected/coreset-{metric}"].tolist()
-    else:
-        pytest.skip(f"golden k-center run has a near-tie (min gap {min(gaps):.2e})")
+    bound = 2 * np.sqrt(512) * 1e-4 * np.abs(e["g"]["embeddings"]).max()
+    assert min(gaps) < bound, f"picked a different set although the golden run has no near-tie (min gap {min(gaps):.2e})"
+    pytest.skip(f"golden k-center run has a near-tie (min top-2 gap {min(gaps):.2e} < {bound:.2e})")
 
 
 def test_kcenter_random_features_exact():
@@ -130,9 +133,11 @@ def test_kcenter_random_features_exact():
             want = S.kcenter_greedy_stream(feats, L, k, metric)
             got = eng.kcenter(torch.from_numpy(feats).to(DEV), L, k, metric).cpu().tolist()
             assert got == want, (D, n, metric)
-    # duplicates: ties resolve to the lowest row, exhausted pool stops early
+    # duplicates: exact ties resolve to the lowest row; a pool with fewer rows than the budget stops early.
+    # (Expectation uses the kernel's difference-form distance: sklearn's xx+yy-2xy form leaves ~1e-7
+    # rounding noise between bit-identical rows, so the reference's order among duplicates is noise.)
     feats = np.repeat(rng.standard_normal((6, 128)).astype(np.float32), 3, axis=0)
-    want = S.kcenter_greedy_stream(feats, 1, 17, "l2")
+    want = S.kcenter_greedy_stream(feats, 1, 17, "l2", row_fn=S.l2_rows_direct)
     assert eng.kcenter(torch.from_numpy(feats).to(DEV), 1, 50, "l2").cpu().tolist() == want
     with pytest.raises(ValueError):
         eng.kcenter(torch.from_numpy(feats).to(DEV), 0, 3, "l2")
@@ -227,7 +232,8 @@ def test_scores_are_chunk_invariant_and_deterministic(env):
     small.load_model(e["sd"])
     c = small.scores(pool, "entropy")
     assert torch.equal(a, c)
-    f32 = pool.float().div(255).unsqueeze(1)          # fp32 [n,1,H,W] input == uint8/255 input
+    # fp32 [n,1,H,W] input (what the reference's datasets hand over: to_tensor on the CPU) == uint8 input
+    f32 = pool.cpu().float().div(255).unsqueeze(1).to(DEV)
     assert torch.equal(a, e["eng"].scores(f32, "entropy"))
     with pytest.raises(RuntimeError, match="max_samples"):
         from b200al import _lib
