@@ -142,6 +142,8 @@ int b200al_conv_time_ms(b200al_ctx* ctx, float* out_ms, int64_t* out_launches, d
 int b200al_debug_layer(b200al_ctx* ctx, int layer_index, int impl, const void* d_in, void* d_out, int n_samples,
                        const float* d_mask, void* stream);
 int b200al_debug_layer_info(b200al_ctx* ctx, int layer_index, int* info /*[12]*/);
+/* per-layer sums of the times folded by the last b200al_conv_time_ms call(s) since b200al_set_timing */
+int b200al_debug_layer_times(b200al_ctx* ctx, float* out_ms, int n);
 
 #ifdef __cplusplus
 }

@@ -66,6 +66,7 @@ PROTOTYPES = {
     "b200al_set_timing": (C.c_int, [C.c_void_p, C.c_int]),
     "b200al_debug_layer": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "b200al_debug_layer_info": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int)]),
+    "b200al_debug_layer_times": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.c_int]),
 }
 
 _lib = None

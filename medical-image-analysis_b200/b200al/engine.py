@@ -294,6 +294,11 @@ class Engine:
         self._check(self.lib.b200al_conv_time_ms(self.ctx, C.byref(ms), C.byref(n), C.byref(fl)))
         return ms.value, n.value, fl.value
 
+    def layer_times_ms(self):
+        arr = (C.c_float * 21)()
+        self._check(self.lib.b200al_debug_layer_times(self.ctx, arr, 21))
+        return list(arr)
+
     # -------------------------------------------------------------- test hook
     def debug_layer_info(self, i: int):
         arr = (C.c_int * 12)()

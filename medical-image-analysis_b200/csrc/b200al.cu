@@ -52,7 +52,7 @@ struct Layer {
   int block = -1;  // PlainBlock index (mask offset source) or -1
   int up = -1;     // upsample index or -1
   int mask_off = 0;
-  int bn = 0, bk = 0, stages = 0;
+  int bn = 0, bk = 0, stages = 0, ctas_per_sm = 1;
   __nv_bfloat16* wp = nullptr;  // packed weights [plane][tap][N][Cin]
   float *scale = nullptr, *bias = nullptr, *shift = nullptr;
   CUtensorMap tmA, tmB;
@@ -94,6 +94,8 @@ struct b200al_ctx {
   long long launches = 0;
   bool timing = false;
   std::vector<cudaEvent_t> ev;
+  std::vector<int> ev_layer;
+  double layer_ms[32] = {0};
   size_t ev_used = 0;
   double conv_ms = 0, conv_flops = 0;
   long long conv_launches = 0, conv_timed = 0;
@@ -233,7 +235,7 @@ ConvKernelFn pick_kernel(int bn, int bk, int nsplit) {
 }
 int stage_bytes(int bn, int bk, int nsplit) { return (nsplit == 3 ? 2 : 1) * (128 * bk * 2 + bn * bk * 2); }
 int conv_smem_bytes(int bn, int bk, int nsplit, int stages) {
-  return stages * stage_bytes(bn, bk, nsplit) + 1024 + 2 * bn * 4 + 1024;
+  return stages * stage_bytes(bn, bk, nsplit) + 1024 + 4 * bn * 4 + 1024;
 }
 
 int env_int(const char* name, int dflt) {
@@ -311,11 +313,15 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
 int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const ConvTcParams& p, int S, cudaStream_t st) {
   ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit);
   if (!fn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no conv kernel for BN=%d BK=%d", L.bn, L.bk);
-  dim3 grid((unsigned)(S * p.tiles_x * p.tiles_y), (unsigned)(p.n_total / L.bn));
+  ConvTcParams q = p;
+  q.n_tiles = p.n_total / L.bn;
+  q.total_tiles = S * p.tiles_x * p.tiles_y * q.n_tiles;
+  const int resident = ctx->sm_count * L.ctas_per_sm;
+  dim3 grid((unsigned)(q.total_tiles < resident ? q.total_tiles : resident));
   const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages);
   const bool t = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
-  if (t) { cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
-  fn<<<grid, kConvThreads, smem, st>>>(tmA, L.tmB, p, L.stages);
+  if (t) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
+  fn<<<grid, kConvThreads, smem, st>>>(tmA, L.tmB, q, L.stages);
   if (t) cudaEventRecord(ctx->ev[ctx->ev_used++], st);
   ctx->launches++;
   ctx->conv_launches++;
@@ -432,6 +438,12 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
     if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d", L.bn, L.bk); b200al_ctx_destroy(ctx); return rc; }
     TRY_CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages)));
+    int occ = 0;
+    TRY_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kConvThreads,
+                                                         conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages)));
+    const int tmem_limit = 512 / (2 * L.bn);  // two accumulator stages per CTA
+    L.ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
+    if (L.ctas_per_sm > 2) L.ctas_per_sm = 2;
   }
   TRY_RC(dev_alloc(ctx, &ctx->first_w, 32 * 9));
   TRY_RC(dev_alloc(ctx, &ctx->first_bias, 32));
@@ -453,6 +465,7 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
   fill_kernel<<<2, 256>>>(ctx->zeros, 0.0f, 512);
   TRY_CU(cudaDeviceSynchronize());
   ctx->ev.resize(2 * 32768);
+  ctx->ev_layer.resize(32768);
   for (auto& e : ctx->ev) TRY_CU(cudaEventCreate(&e));
 #undef TRY_RC
 #undef TRY_CU
@@ -814,6 +827,7 @@ extern "C" int b200al_set_timing(b200al_ctx* ctx, int enable) {
   ctx->conv_flops = 0;
   ctx->conv_launches = 0;
   ctx->conv_timed = 0;
+  memset(ctx->layer_ms, 0, sizeof(ctx->layer_ms));
   return B200AL_OK;
 }
 
@@ -826,6 +840,7 @@ extern "C" int b200al_conv_time_ms(b200al_ctx* ctx, float* out_ms, int64_t* out_
     float ms = 0.f;
     CUDA_TRY(ctx, cudaEventElapsedTime(&ms, ctx->ev[i], ctx->ev[i + 1]));
     ctx->conv_ms += ms;
+    ctx->layer_ms[ctx->ev_layer[i / 2] & 31] += ms;
   }
   ctx->ev_used = 0;
   *out_ms = (float)ctx->conv_ms;
@@ -837,6 +852,12 @@ extern "C" int b200al_conv_time_ms(b200al_ctx* ctx, float* out_ms, int64_t* out_
 // ---------------------------------------------------------------------------
 // test hooks
 // ---------------------------------------------------------------------------
+extern "C" int b200al_debug_layer_times(b200al_ctx* ctx, float* out_ms, int n) {
+  if (!ctx || !out_ms) return B200AL_ERR_ARG;
+  for (int i = 0; i < n && i < 32; ++i) out_ms[i] = (float)ctx->layer_ms[i];
+  return B200AL_OK;
+}
+
 // info: kind, cin, cout, stride, inH, inW, in_pitch, in_c_off, outH, outW, out_pitch, out_c_off
 extern "C" int b200al_debug_layer_info(b200al_ctx* ctx, int layer_index, int* info) {
   if (!ctx || !info || layer_index < 0 || layer_index >= (int)ctx->layers.size()) return B200AL_ERR_ARG;

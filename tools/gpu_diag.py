@@ -98,7 +98,14 @@ def perf(precision, chunk=64, n=256, T=1):
     eng.set_timing(True)
     eng.scores(imgs, "entropy", T=T, drop_p=p, seed=1)
     cms, cn, cfl = eng.conv_time_ms()
+    lt = eng.layer_times_ms()
     eng.set_timing(False)
+    for i, ms_l in enumerate(lt):
+        info = eng.debug_layer_info(i)
+        px = info["outH"] * info["outW"] if info["kind"] == 0 else info["inH"] * info["inW"] * 4
+        fl_l = 2.0 * px * info["cout"] * info["cin"] * (9 if info["kind"] == 0 else 1) * n * T
+        print(f"  layer {i:2d} kind={info['kind']} {info['cin']:3d}->{info['cout']:3d} s{info['stride']} out {info['outH']:3d}: "
+              f"{ms_l * 1e3 / (n * T):7.2f} us/sample {fl_l / ms_l / 1e9:6.1f} TF", flush=True)
     print(f"conv kernels: {cms:.2f} ms over {cn} launches, {cfl / cms / 1e9:.1f} TFLOP/s algorithmic", flush=True)
     e0.record()
     eng.embed(imgs)
