@@ -52,10 +52,10 @@ struct Layer {
   int block = -1;  // PlainBlock index (mask offset source) or -1
   int up = -1;     // upsample index or -1
   int mask_off = 0;
-  int bn = 0, bk = 0, stages = 0, ctas_per_sm = 1;
+  int bn = 0, bk = 0, stages = 0, ctas_per_sm = 1, cw = 32, nbuf = 1, ngroups = 2;
   __nv_bfloat16* wp = nullptr;  // packed weights [plane][tap][N][Cin]
   float *scale = nullptr, *bias = nullptr, *shift = nullptr;
-  CUtensorMap tmA, tmB;
+  CUtensorMap tmA, tmB, tmO;
   ConvTcParams p;
   double flops_per_sample = 0;
 };
@@ -213,29 +213,38 @@ int make_tma_wgt(b200al_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, in
 // ---------------------------------------------------------------------------
 // tcgen05 conv dispatch
 // ---------------------------------------------------------------------------
-typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const ConvTcParams, const int);
+typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const ConvTcParams, const int,
+                             const int, const int);
 
-template <int BN, int BK>
+template <int BN, int BK, int CW>
 ConvKernelFn pick_split(int nsplit) {
-  return nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<BN, BK, 3> : (ConvKernelFn)conv_tc_kernel<BN, BK, 1>;
+  return nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<BN, BK, 3, CW> : (ConvKernelFn)conv_tc_kernel<BN, BK, 1, CW>;
 }
-ConvKernelFn pick_kernel(int bn, int bk, int nsplit) {
+template <int BN, int BK>
+ConvKernelFn pick_cw(int nsplit, int cw) {
+  if constexpr (BN >= 64) {
+    if (cw == 64) return pick_split<BN, BK, 64>(nsplit);
+  }
+  return cw == 32 ? pick_split<BN, BK, 32>(nsplit) : nullptr;
+}
+ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw) {
   if (bk == 32) {
-    if (bn == 32) return pick_split<32, 32>(nsplit);
-    if (bn == 64) return pick_split<64, 32>(nsplit);
+    if (bn == 32) return pick_cw<32, 32>(nsplit, cw);
+    if (bn == 64) return pick_cw<64, 32>(nsplit, cw);
     return nullptr;
   }
   switch (bn) {
-    case 32: return pick_split<32, 64>(nsplit);
-    case 64: return pick_split<64, 64>(nsplit);
-    case 128: return pick_split<128, 64>(nsplit);
-    case 256: return pick_split<256, 64>(nsplit);
+    case 32: return pick_cw<32, 64>(nsplit, cw);
+    case 64: return pick_cw<64, 64>(nsplit, cw);
+    case 128: return pick_cw<128, 64>(nsplit, cw);
+    case 256: return pick_cw<256, 64>(nsplit, cw);
   }
   return nullptr;
 }
 int stage_bytes(int bn, int bk, int nsplit) { return (nsplit == 3 ? 2 : 1) * (128 * bk * 2 + bn * bk * 2); }
-int conv_smem_bytes(int bn, int bk, int nsplit, int stages) {
-  return stages * stage_bytes(bn, bk, nsplit) + 1024 + 4 * bn * 4 + 1024;
+int out_buf_bytes(int cw, int nsplit) { return (nsplit == 3 ? 2 : 1) * 128 * cw * 2; }
+int conv_smem_bytes(int bn, int bk, int nsplit, int stages, int cw, int nbufs_total) {
+  return stages * stage_bytes(bn, bk, nsplit) + nbufs_total * out_buf_bytes(cw, nsplit) + 1024 + 8 * bn * 4;
 }
 
 int env_int(const char* name, int dflt) {
@@ -263,10 +272,27 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   L.bn = n_total < bn_max ? n_total : bn_max;
   if (L.kind == KIND_CONVT && L.bn > L.cout && (L.bn % L.cout) != 0) L.bn = L.cout;
   if (L.bk == 32 && L.bn > 64) L.bn = 64;
+  // smem policy: small tiles aim for 2 CTAs/SM (<= ~110 KB each), large ones take the whole SM.
   const int sb = stage_bytes(L.bn, L.bk, ctx->nsplit);
-  const int budget = env_int("B200AL_SMEM_BUDGET", 98304);
-  int st = budget / sb;
-  if (st < 2) st = (200 * 1024) / sb;
+  const int kMaxSmem = 227 * 1024;
+  const int fixed = 1024 + 8 * L.bn * 4;
+  L.cw = (L.bn >= 64 && L.cout >= 64) ? 64 : 32;
+  L.cw = env_int("B200AL_CW", L.cw) == 32 ? 32 : L.cw;
+  // Short k-loops (full-resolution layers, transposed convs) are epilogue-heavy: two epilogue groups.
+  // Long k-loops are MMA-bound: one group, the shared memory goes to pipeline stages instead.
+  const int num_kb = (L.kind == KIND_CONV3 ? 9 : 1) * (L.cin / L.bk);
+  L.ngroups = env_int("B200AL_NGROUPS", num_kb <= 18 ? 2 : 1);
+  L.nbuf = L.ngroups == 2 ? 1 : 2;
+  const int budget2 = env_int("B200AL_SMEM_BUDGET", 110 * 1024);
+  int st = (budget2 - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
+  if (st < 3) {  // one CTA per SM
+    st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
+    if (st < 3 && L.ngroups * L.nbuf > 1) {
+      if (L.ngroups == 1) L.nbuf = 1;
+      st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
+    }
+    if (st < 3 && L.cw == 64) { L.cw = 32; st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(32, ctx->nsplit)) / sb; }
+  }
   if (st > 8) st = 8;
   if (st < 2) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "conv tile does not fit shared memory");
   L.stages = st;
@@ -276,6 +302,8 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   p.a_lo_off = ib.c_total;
   const int gridW = L.kind == KIND_CONV3 ? outW : inW, gridH = L.kind == KIND_CONV3 ? outH : inH;
   choose_tile(gridW, &p.tw, &p.th);
+  if (p.tw != 16 || p.th != 8)
+    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "image width %d too small for the 8x16 output tile", ctx->W);
   if (gridW % p.tw || gridH % p.th)
     return set_err(ctx, B200AL_ERR_UNSUPPORTED, "image size %dx%d not tileable at level %d", ctx->H, ctx->W, ob.level);
   p.tiles_x = gridW / p.tw;
@@ -310,18 +338,19 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   return 0;
 }
 
-int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const ConvTcParams& p, int S, cudaStream_t st) {
-  ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit);
+int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtensorMap& tmO, const ConvTcParams& p, int S,
+                cudaStream_t st) {
+  ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw);
   if (!fn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no conv kernel for BN=%d BK=%d", L.bn, L.bk);
   ConvTcParams q = p;
   q.n_tiles = p.n_total / L.bn;
   q.total_tiles = S * p.tiles_x * p.tiles_y * q.n_tiles;
   const int resident = ctx->sm_count * L.ctas_per_sm;
   dim3 grid((unsigned)(q.total_tiles < resident ? q.total_tiles : resident));
-  const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages);
+  const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups);
   const bool t = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
   if (t) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
-  fn<<<grid, kConvThreads, smem, st>>>(tmA, L.tmB, q, L.stages);
+  fn<<<grid, kConvThreads, smem, st>>>(tmA, L.tmB, tmO, q, L.stages, L.nbuf, L.ngroups);
   if (t) cudaEventRecord(ctx->ev[ctx->ev_used++], st);
   ctx->launches++;
   ctx->conv_launches++;
@@ -434,16 +463,22 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
                         L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw, L.p.th));
     // rows: conv [2 planes][9 taps][Cout]; convT [2 planes][1][4*Cout]
     TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn));
-    ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit);
-    if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d", L.bn, L.bk); b200al_ctx_destroy(ctx); return rc; }
-    TRY_CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages)));
+    const ActBuf& ob = ctx->bufs[L.out.buf];
+    // output map: box = one epilogue warp's 2 image rows x 16 px x CW channels; transposed conv uses the stride-2 view
+    TRY_RC(make_tma_act(ctx, &L.tmO, ob.ptr, max_samples, H >> ob.level, W >> ob.level, 2 * ob.c_total,
+                        L.kind == KIND_CONVT ? 2 : 1, L.cw, 16, 2));
+    ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw);
+    if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d CW=%d", L.bn, L.bk, L.cw); b200al_ctx_destroy(ctx); return rc; }
+    const int smem_l = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups);
+    TRY_CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     int occ = 0;
-    TRY_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kConvThreads,
-                                                         conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages)));
+    TRY_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kConvThreads, smem_l));
     const int tmem_limit = 512 / (2 * L.bn);  // two accumulator stages per CTA
     L.ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
     if (L.ctas_per_sm > 2) L.ctas_per_sm = 2;
+    if (env_int("B200AL_VERBOSE", 0))
+      fprintf(stderr, "b200al plan: kind=%d %d->%d s%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d\n", L.kind,
+              L.cin, L.cout, L.stride, L.bn, L.bk, L.stages, L.cw, L.nbuf, L.ngroups, smem_l, L.ctas_per_sm);
   }
   TRY_RC(dev_alloc(ctx, &ctx->first_w, 32 * 9));
   TRY_RC(dev_alloc(ctx, &ctx->first_bias, 32));
@@ -499,6 +534,8 @@ extern "C" int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, voi
   if (!ctx || !w) return set_err(ctx, B200AL_ERR_ARG, "NULL argument");
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (!(w->leaky_slope >= 0.f && w->leaky_slope <= 1.f))
+    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "LeakyReLU slope %g outside [0,1]", (double)w->leaky_slope);
   ctx->slope = w->leaky_slope;
   const b200al_block_weights& b0 = w->blocks[0];
   if (!b0.d_conv_weight || !w->d_head_weight || !w->d_head_bias) return set_err(ctx, B200AL_ERR_ARG, "NULL weight pointer");
@@ -565,7 +602,7 @@ int run_layers(b200al_ctx* ctx, int n_layers, int S, const float* mask, cudaStre
     Layer& L = ctx->layers[i];
     ConvTcParams p = L.p;
     p.mask = (mask && L.kind == KIND_CONV3) ? mask + L.mask_off : nullptr;
-    int rc = launch_conv(ctx, L, L.tmA, p, S, st);
+    int rc = launch_conv(ctx, L, L.tmA, L.tmO, p, S, st);
     if (rc) return rc;
   }
   return 0;
@@ -888,10 +925,14 @@ extern "C" int b200al_debug_layer(b200al_ctx* ctx, int layer_index, int impl, co
     int rc = make_tma_act(ctx, &tmA, (const __nv_bfloat16*)d_in, n_samples, inH, inW, 2 * ib.c_total,
                           L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw, L.p.th);
     if (rc) return rc;
+    CUtensorMap tmO;
+    rc = make_tma_act(ctx, &tmO, (const __nv_bfloat16*)d_out, n_samples, ctx->H >> ob.level, ctx->W >> ob.level,
+                      2 * ob.c_total, L.kind == KIND_CONVT ? 2 : 1, L.cw, 16, 2);
+    if (rc) return rc;
     ConvTcParams p = L.p;
     p.out = (__nv_bfloat16*)d_out;
     p.mask = mask;
-    return launch_conv(ctx, L, tmA, p, n_samples, st);
+    return launch_conv(ctx, L, tmA, tmO, p, n_samples, st);
   }
   ConvSimtParams q;
   q.in = (const __nv_bfloat16*)d_in + L.in.c_off;

@@ -53,16 +53,18 @@ struct ConvTcParams {
   int write_lo;
 };
 
-constexpr int kConvThreads = 192;
+constexpr int kConvThreads = 320;  // TMA warp + MMA warp + 2 epilogue groups of 4 warps
 
-template <int BLOCK_N, int BK, int NSPLIT>
+// smem: [stages x (A planes, B planes)] [nbuf x planes x 128 x CW staging for the TMA store] [barriers] [affine]
+template <int BLOCK_N, int BK, int NSPLIT, int CW>
 struct ConvTcSmem {
   static constexpr int kPlanes = (NSPLIT == 3) ? 2 : 1;
   static constexpr int kABytes = 128 * BK * 2;
   static constexpr int kBBytes = BLOCK_N * BK * 2;
   static constexpr int kStageBytes = kPlanes * (kABytes + kBBytes);
-  static constexpr int kTailBytes = 1024;  // barriers, tmem ptr, epilogue affine
-  static constexpr int bytes(int stages) { return stages * kStageBytes + kTailBytes + 4 * BLOCK_N * 4 + 1024; }
+  static constexpr int kOutWarpBytes = 32 * CW * 2;                  // one warp's 32 rows of one plane
+  static constexpr int kOutBufBytes = kPlanes * 4 * kOutWarpBytes;   // one staging buffer
+  static constexpr int kTailBytes = 1024;  // barriers, tmem ptr
 };
 
 struct TileCoord {
@@ -82,32 +84,39 @@ __device__ __forceinline__ TileCoord decode_tile(const ConvTcParams& p, int t, i
   return c;
 }
 
-template <int BLOCK_N, int BK, int NSPLIT>
+template <int BLOCK_N, int BK, int NSPLIT, int CW>
 __global__ void __launch_bounds__(kConvThreads)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const ConvTcParams p, const int stages) {
-  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT>;
+               const __grid_constant__ CUtensorMap tmO, const ConvTcParams p, const int stages, const int nbuf, const int ngroups) {
+  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW>;
+  static_assert(BLOCK_N % CW == 0 && (CW == 32 || CW == 64), "bad store chunk width");
   constexpr uint32_t kRowBytes = BK * 2;  // 128 -> SW128, 64 -> SW64
   constexpr uint32_t kTmemCols = 2 * BLOCK_N;  // two accumulator stages (power of two >= 64)
-  extern __shared__ uint8_t smem_raw[];
-  // 1024-byte alignment for the swizzled tiles
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint8_t* tail = smem + (size_t)stages * L::kStageBytes;
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  // 1024-byte alignment for the swizzled tiles (checked below; the host adds no slack)
+  uint8_t* smem = smem_raw;
+  uint8_t* staging = smem + (size_t)stages * L::kStageBytes;  // 1024-aligned (stage bytes are a multiple of 1024)
+  uint8_t* tail = staging + (size_t)ngroups * nbuf * L::kOutBufBytes;  // epilogue groups x nbuf buffers
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
   uint64_t* empty_bar = full_bar + 16;
   uint64_t* tfull_bar = empty_bar + 16;   // [2] accumulator ready
   uint64_t* tempty_bar = tfull_bar + 2;   // [2] accumulator drained
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-  float* es = reinterpret_cast<float*>(tail + L::kTailBytes);  // [2][BLOCK_N]
-  float* eh = es + 2 * BLOCK_N;                                // [2][BLOCK_N]
+  float* es = reinterpret_cast<float*>(tail + L::kTailBytes);  // [2 groups][2][BLOCK_N]
+  float* eh = es + 4 * BLOCK_N;                                // [2 groups][2][BLOCK_N]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
   const int num_kb = p.taps * p.chunks;
 
   if (warp == 0 && lane == 0) {
+    if (smem_u32(smem) & 1023u) {
+      printf("b200al: dynamic shared memory is not 1024-byte aligned\n");
+      __trap();
+    }
     tma_prefetch_desc(&tmA);
     tma_prefetch_desc(&tmB);
+    tma_prefetch_desc(&tmO);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < stages; ++i) {
@@ -194,16 +203,22 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const int et = threadIdx.x - 64;  // 0..127
-    const int q = warp & 3;           // TMEM lane quarter this warp may read
-    const int row = q * 32 + lane;
-    const int ry = row / p.tw, rx = row - ry * p.tw;
-    uint32_t acc = 0, acc_phase = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+    // ===================== epilogue: two groups of 4 warps =====================
+    // Group g (warps 2+4g .. 5+4g) drains accumulator stage g, i.e. every other tile of this CTA,
+    // so the affine/activation/split math of two tiles runs concurrently.
+    const int group = (warp - 2) >> 2;
+    const int et = (threadIdx.x - 64) & 127;  // 0..127 within the group
+    const int q = warp & 3;                   // TMEM lane quarter this warp may read
+    int obuf = 0, ebuf = 0;
+    uint8_t* gstaging = staging + (size_t)group * nbuf * L::kOutBufBytes;
+    int it = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+      if (group >= ngroups || (ngroups == 2 && (it & 1) != group)) continue;
+      const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
       const TileCoord tc = decode_tile(p, t, BLOCK_N);
-      float* esa = es + acc * BLOCK_N;
-      float* eha = eh + acc * BLOCK_N;
+      float* esa = es + (group * 2 + ebuf) * BLOCK_N;
+      float* eha = eh + (group * 2 + ebuf) * BLOCK_N;
+      ebuf ^= 1;
       for (int i = et; i < BLOCK_N; i += 128) {
         const int n = tc.n0 + i;
         const int c = p.shuffle ? (n % p.cout) : n;
@@ -212,52 +227,78 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         esa[i] = sc;
         eha[i] = p.bias[c] * sc + p.shift[c];
       }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
+      if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");
+      else asm volatile("bar.sync 2, 128;" ::: "memory");
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
 #pragma unroll 1
-      for (int c0 = 0; c0 < BLOCK_N; c0 += 32) {
-        uint32_t v[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BLOCK_N + c0), v);
-        tmem_ld_wait();
-        if (c0 + 32 >= BLOCK_N) {  // last read of this accumulator: hand it back to the MMA warp
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+      for (int c0 = 0; c0 < BLOCK_N; c0 += CW) {
+        // staging buffer `obuf` must no longer be read by an earlier TMA store of this warp
+        if (lane == 0) {
+          if (nbuf == 1) tma_store_wait_read<0>(); else tma_store_wait_read<1>();
         }
-        int oy = tc.y0 + ry, ox = tc.x0 + rx, cbase = tc.n0 + c0;
-        if (p.shuffle) {
-          const int quad = cbase / p.cout;
-          cbase -= quad * p.cout;
-          oy = 2 * oy + (quad >> 1);
-          ox = 2 * ox + (quad & 1);
-        }
-        __nv_bfloat16* dst =
-            p.out + ((size_t)((size_t)tc.sample * p.out_H + oy) * p.out_W + ox) * p.out_pitch + cbase;
-        uint32_t hi[16], lo[16];
+        __syncwarp();
+        uint8_t* sub_hi = gstaging + (size_t)obuf * L::kOutBufBytes + (size_t)q * L::kOutWarpBytes;
+        uint8_t* sub_lo = sub_hi + 4 * L::kOutWarpBytes;
 #pragma unroll
-        for (int j = 0; j < 16; ++j) {
-          const float y0f = leaky(__uint_as_float(v[2 * j]) * esa[c0 + 2 * j] + eha[c0 + 2 * j], p.slope);
-          const float y1f =
-              leaky(__uint_as_float(v[2 * j + 1]) * esa[c0 + 2 * j + 1] + eha[c0 + 2 * j + 1], p.slope);
-          __nv_bfloat16 h0, l0, h1, l1;
-          split_bf16(y0f, h0, l0);
-          split_bf16(y1f, h1, l1);
-          hi[j] = pack_bf16x2(h0, h1);
-          lo[j] = pack_bf16x2(l0, l1);
-        }
-        uint4* dh = reinterpret_cast<uint4*>(dst + p.out_hi_off);
+        for (int h = 0; h < CW / 32; ++h) {
+          uint32_t v[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BLOCK_N + c0 + h * 32), v);
+          tmem_ld_wait();
+          if (c0 + CW >= BLOCK_N && h == CW / 32 - 1) {  // last read of this accumulator: hand it back
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+          }
+          uint32_t hi[16], lo[16];
 #pragma unroll
-        for (int j = 0; j < 4; ++j) dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
-        if (p.write_lo) {
-          uint4* dl = reinterpret_cast<uint4*>(dst + p.out_lo_off);
+          for (int j = 0; j < 16; ++j) {
+            const int cc = c0 + h * 32 + 2 * j;
+            const float2 sc2 = *reinterpret_cast<const float2*>(esa + cc);
+            const float2 sh2 = *reinterpret_cast<const float2*>(eha + cc);
+            float y0f = fmaf(__uint_as_float(v[2 * j]), sc2.x, sh2.x);
+            float y1f = fmaf(__uint_as_float(v[2 * j + 1]), sc2.y, sh2.y);
+            y0f = fmaxf(y0f, y0f * p.slope);  // LeakyReLU for 0 <= slope <= 1 (checked on the host)
+            y1f = fmaxf(y1f, y1f * p.slope);
+            const __nv_bfloat162 h2 = __floats2bfloat162_rn(y0f, y1f);
+            const uint32_t hb = *reinterpret_cast<const uint32_t*>(&h2);
+            hi[j] = hb;
+            if (NSPLIT == 3) {
+              const __nv_bfloat162 l2 =
+                  __floats2bfloat162_rn(y0f - __uint_as_float(hb << 16), y1f - __uint_as_float(hb & 0xffff0000u));
+              lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
+            }
+          }
+          // swizzled row-major staging: row = lane, 16-byte chunk j of the row at (j ^ swz)
 #pragma unroll
-          for (int j = 0; j < 4; ++j) dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+          for (int j = 0; j < 4; ++j) {
+            const int chunk = h * 4 + j;
+            const uint32_t off = (CW == 64) ? (uint32_t)(lane * 128 + ((chunk ^ (lane & 7)) << 4))
+                                            : (uint32_t)(lane * 64 + ((chunk ^ ((lane >> 1) & 3)) << 4));
+            *reinterpret_cast<uint4*>(sub_hi + off) = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+            if (NSPLIT == 3)
+              *reinterpret_cast<uint4*>(sub_lo + off) =
+                  make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+          }
         }
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          int cbase = tc.n0 + c0, cx = tc.x0, cp = 0, cy = tc.y0 + 2 * q, coff = 0;
+          if (p.shuffle) {  // stride-2 view of the output: (2*pitch, W/2, 2, H/2, S)
+            const int quad = cbase / p.cout;
+            cbase -= quad * p.cout;
+            coff = (quad & 1) * (int)p.out_pitch;
+            cp = quad >> 1;
+          }
+          tma_store_5d(&tmO, smem_u32(sub_hi), coff + p.out_hi_off + cbase, cx, cp, cy, tc.sample);
+          if (NSPLIT == 3) tma_store_5d(&tmO, smem_u32(sub_lo), coff + p.out_lo_off + cbase, cx, cp, cy, tc.sample);
+          tma_store_commit();
+        }
+        if (++obuf == nbuf) obuf = 0;
       }
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
     }
+    if (lane == 0) tma_store_wait_all();  // all output tiles of this warp have landed
   }
   tc_fence_before();
   __syncthreads();
