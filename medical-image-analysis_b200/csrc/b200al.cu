@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "conv_fold.cuh"
 #include "conv_tc.cuh"
 #include "kcenter.cuh"
 #include "topk.cuh"
@@ -57,6 +58,9 @@ struct Layer {
   float *scale = nullptr, *bias = nullptr, *shift = nullptr;
   CUtensorMap tmA, tmB, tmO;
   ConvTcParams p;
+  bool fold = false;   // column-folded kernel (conv_fold.cuh): stride-1 3x3, Cout = 32, Cin in {32, 64}
+  ConvFoldParams fp;
+  int slots = 0;
   double flops_per_sample = 0;
 };
 
@@ -247,6 +251,17 @@ int conv_smem_bytes(int bn, int bk, int nsplit, int stages, int cw, int nbufs_to
   return stages * stage_bytes(bn, bk, nsplit) + nbufs_total * out_buf_bytes(cw, nsplit) + 1024 + 8 * bn * 4;
 }
 
+typedef void (*FoldKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const ConvFoldParams, const int);
+FoldKernelFn pick_fold_kernel(int cin, int nsplit) {
+  if (cin == 32) return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<32, 3> : (FoldKernelFn)conv_fold_kernel<32, 1>;
+  if (cin == 64) return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<64, 3> : (FoldKernelFn)conv_fold_kernel<64, 1>;
+  return nullptr;
+}
+int fold_smem_bytes(int cin, int nsplit, int slots) {
+  const int planes = nsplit == 3 ? 2 : 1;
+  return planes * 3 * kFoldN * cin * 2 + slots * 6 * 32 * cin * 2 + 8 * planes * 2048 + 2048;
+}
+
 int env_int(const char* name, int dflt) {
   const char* v = getenv(name);
   return v ? atoi(v) : dflt;
@@ -322,6 +337,26 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
       p.a_dy[i] = (i == 0) ? -1 : 0;
     }
   }
+  L.fold = L.kind == KIND_CONV3 && L.stride == 1 && L.cout == 32 && (L.cin == 32 || L.cin == 64) &&
+           outH % 4 == 0 && env_int("B200AL_FOLD", 1) != 0;
+  if (L.fold) {
+    ConvFoldParams& f = L.fp;
+    memset(&f, 0, sizeof(f));
+    f.a_c0 = L.in.c_off;
+    f.a_lo_off = ib.c_total;
+    f.tiles_x = (outW + kFoldValid - 1) / kFoldValid;
+    f.tiles_y = outH / 4;
+    f.slope = ctx->slope;
+    f.out_hi_off = L.out.c_off;
+    f.out_lo_off = ob.c_total + L.out.c_off;
+    f.mask_stride = B200AL_MASK_CHANNELS;
+    int sl = 16;
+    while (sl > 2 && fold_smem_bytes(L.cin, ctx->nsplit, sl) > kMaxSmem) --sl;
+    sl = env_int("B200AL_FOLD_SLOTS", sl);
+    if (sl < 2 || sl > 16 || fold_smem_bytes(L.cin, ctx->nsplit, sl) > kMaxSmem)
+      return set_err(ctx, B200AL_ERR_UNSUPPORTED, "folded conv tile does not fit shared memory");
+    L.slots = sl;
+  }
   p.slope = L.kind == KIND_CONV3 ? ctx->slope : 1.0f;
   p.out = ob.ptr;
   p.out_pitch = out_pitch;
@@ -338,8 +373,44 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   return 0;
 }
 
+// TMA maps of a layer for given input / output base pointers (the context's own buffers, or a test's).
+int make_layer_maps(b200al_ctx* ctx, const Layer& L, const __nv_bfloat16* in, const __nv_bfloat16* out, int S,
+                    CUtensorMap* tmA, CUtensorMap* tmO) {
+  const ActBuf& ib = ctx->bufs[L.in.buf];
+  const ActBuf& ob = ctx->bufs[L.out.buf];
+  const int inH = ctx->H >> ib.level, inW = ctx->W >> ib.level;
+  const int outH = ctx->H >> ob.level, outW = ctx->W >> ob.level;
+  int rc;
+  if (L.fold) {
+    // A: 6-row x 32-column halo box, all Cin channels of one plane; O: one image row of 30 pixels x 32 channels
+    if ((rc = make_tma_act(ctx, tmA, in, S, inH, inW, 2 * ib.c_total, 1, L.cin, 32, 6))) return rc;
+    return make_tma_act(ctx, tmO, out, S, outH, outW, 2 * ob.c_total, 1, 32, kFoldValid, 1);
+  }
+  if ((rc = make_tma_act(ctx, tmA, in, S, inH, inW, 2 * ib.c_total, L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw,
+                         L.p.th)))
+    return rc;
+  // output map: box = one epilogue warp's 2 image rows x 16 px x CW channels; transposed conv uses the stride-2 view
+  return make_tma_act(ctx, tmO, out, S, outH, outW, 2 * ob.c_total, L.kind == KIND_CONVT ? 2 : 1, L.cw, 16, 2);
+}
+
 int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtensorMap& tmO, const ConvTcParams& p, int S,
                 cudaStream_t st) {
+  if (L.fold) {
+    FoldKernelFn ffn = pick_fold_kernel(L.cin, ctx->nsplit);
+    ConvFoldParams f = L.fp;
+    f.scale = p.scale; f.bias = p.bias; f.shift = p.shift; f.mask = p.mask; f.slope = p.slope;
+    f.total_tiles = S * f.tiles_x * f.tiles_y;
+    dim3 fgrid((unsigned)(f.total_tiles < ctx->sm_count ? f.total_tiles : ctx->sm_count));
+    const int fsmem = fold_smem_bytes(L.cin, ctx->nsplit, L.slots);
+    const bool ft = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
+    if (ft) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
+    ffn<<<fgrid, kFoldThreads, fsmem, st>>>(tmA, L.tmB, tmO, f, L.slots);
+    if (ft) cudaEventRecord(ctx->ev[ctx->ev_used++], st);
+    ctx->launches++;
+    ctx->conv_launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return 0;
+  }
   ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw);
   if (!fn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no conv kernel for BN=%d BK=%d", L.bn, L.bk);
   ConvTcParams q = p;
@@ -458,15 +529,19 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
     TRY_RC(dev_alloc(ctx, &L.scale, (size_t)L.cout));
     TRY_RC(dev_alloc(ctx, &L.bias, (size_t)L.cout));
     TRY_RC(dev_alloc(ctx, &L.shift, (size_t)L.cout));
-    const ActBuf& ib = ctx->bufs[L.in.buf];
-    TRY_RC(make_tma_act(ctx, &L.tmA, ib.ptr, max_samples, H >> ib.level, W >> ib.level, 2 * ib.c_total,
-                        L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw, L.p.th));
+    TRY_RC(make_layer_maps(ctx, L, ctx->bufs[L.in.buf].ptr, ctx->bufs[L.out.buf].ptr, max_samples, &L.tmA, &L.tmO));
+    if (L.fold) {
+      // weights: rows [2 planes][9 taps][32], box = the three column taps of one filter row (96 rows) x Cin
+      TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * 9 * L.cout, L.cin, L.cin, kFoldN));
+      FoldKernelFn ffn = pick_fold_kernel(L.cin, ctx->nsplit);
+      TRY_CU(cudaFuncSetAttribute(ffn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+      if (env_int("B200AL_VERBOSE", 0))
+        fprintf(stderr, "b200al plan: fold %d->%d slots=%d smem=%d\n", L.cin, L.cout, L.slots,
+                fold_smem_bytes(L.cin, ctx->nsplit, L.slots));
+      continue;
+    }
     // rows: conv [2 planes][9 taps][Cout]; convT [2 planes][1][4*Cout]
     TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn));
-    const ActBuf& ob = ctx->bufs[L.out.buf];
-    // output map: box = one epilogue warp's 2 image rows x 16 px x CW channels; transposed conv uses the stride-2 view
-    TRY_RC(make_tma_act(ctx, &L.tmO, ob.ptr, max_samples, H >> ob.level, W >> ob.level, 2 * ob.c_total,
-                        L.kind == KIND_CONVT ? 2 : 1, L.cw, 16, 2));
     ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw);
     if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d CW=%d", L.bn, L.bk, L.cw); b200al_ctx_destroy(ctx); return rc; }
     const int smem_l = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups);
@@ -921,13 +996,8 @@ extern "C" int b200al_debug_layer(b200al_ctx* ctx, int layer_index, int impl, co
   const int inH = ctx->H >> ib.level, inW = ctx->W >> ib.level;
   const float* mask = (d_mask && L.kind == KIND_CONV3) ? d_mask + L.mask_off : nullptr;
   if (impl == 0) {
-    CUtensorMap tmA;
-    int rc = make_tma_act(ctx, &tmA, (const __nv_bfloat16*)d_in, n_samples, inH, inW, 2 * ib.c_total,
-                          L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw, L.p.th);
-    if (rc) return rc;
-    CUtensorMap tmO;
-    rc = make_tma_act(ctx, &tmO, (const __nv_bfloat16*)d_out, n_samples, ctx->H >> ob.level, ctx->W >> ob.level,
-                      2 * ob.c_total, L.kind == KIND_CONVT ? 2 : 1, L.cw, 16, 2);
+    CUtensorMap tmA, tmO;
+    int rc = make_layer_maps(ctx, L, (const __nv_bfloat16*)d_in, (const __nv_bfloat16*)d_out, n_samples, &tmA, &tmO);
     if (rc) return rc;
     ConvTcParams p = L.p;
     p.out = (__nv_bfloat16*)d_out;
