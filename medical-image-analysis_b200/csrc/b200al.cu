@@ -350,6 +350,7 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
     f.out_hi_off = L.out.c_off;
     f.out_lo_off = ob.c_total + L.out.c_off;
     f.mask_stride = B200AL_MASK_CHANNELS;
+    f.dbg = env_int("B200AL_FOLD_DBG", 0);
     int sl = 16;
     while (sl > 2 && fold_smem_bytes(L.cin, ctx->nsplit, sl) > kMaxSmem) --sl;
     sl = env_int("B200AL_FOLD_SLOTS", sl);

@@ -174,6 +174,21 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, uint32_t 
          (sbo << 32) | (1ull << 46) /*descriptor version (sm_100)*/ | (layout << 61);
 }
 
+// The same descriptor split in two 32-bit halves: `hi` is a per-kernel constant, `lo` carries the
+// start address (>> 4) and can be advanced with plain 32-bit adds (no carry out of the 14-bit field
+// as long as the operand stays inside the 256 KB shared-memory window).
+__host__ __device__ constexpr uint32_t umma_smem_desc_hi(uint32_t row_bytes) {
+  return ((8u * row_bytes) >> 4) | (1u << 14) | ((row_bytes == 128 ? 2u : (row_bytes == 64 ? 4u : 6u)) << 29);
+}
+__device__ __forceinline__ uint32_t umma_smem_desc_lo(uint32_t smem_addr) {
+  return ((smem_addr & 0x3FFFF) >> 4) | (1u << 16);
+}
+__device__ __forceinline__ uint64_t make_desc(uint32_t lo, uint32_t hi) {
+  uint64_t d;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(d) : "r"(lo), "r"(hi));
+  return d;
+}
+
 // 32 lanes x 32 consecutive fp32 columns: thread i of the warp gets TMEM lane
 // (lane_base + i), registers = columns.
 __device__ __forceinline__ void tmem_ld_32x32(uint32_t taddr, uint32_t (&v)[32]) {

@@ -40,12 +40,37 @@ struct ConvFoldParams {
   int mask_stride;
   float slope;
   int out_hi_off, out_lo_off;
+  int dbg;  // timing experiments only (B200AL_FOLD_DBG): 1 = no MMAs, 2 = no epilogue math/stores, 4 = no TMA stores
 };
 
 constexpr int kFoldThreads = 320;   // TMA warp, MMA warp, 2 epilogue groups of 4 warps
 constexpr int kFoldN = 96;          // 3 column taps x 32 output channels
 constexpr int kFoldValid = 30;      // output columns per tile
 constexpr int kFoldAccStride = 128; // TMEM columns between the two accumulators
+
+// Each persistent CTA owns a contiguous range of tiles (sample-major, then tile row, then tile
+// column) and steps through it without divisions.
+struct FoldTileWalk {
+  int t, t_end, sample, ty, tx;
+  __device__ __forceinline__ void init(const ConvFoldParams& p) {
+    const long long total = p.total_tiles;
+    t = (int)(total * blockIdx.x / gridDim.x);
+    t_end = (int)(total * (blockIdx.x + 1) / gridDim.x);
+    const int tps = p.tiles_x * p.tiles_y;
+    sample = t / tps;
+    const int rem = t - sample * tps;
+    ty = rem / p.tiles_x;
+    tx = rem - ty * p.tiles_x;
+  }
+  __device__ __forceinline__ bool valid() const { return t < t_end; }
+  __device__ __forceinline__ void next(const ConvFoldParams& p) {
+    ++t;
+    if (++tx == p.tiles_x) {
+      tx = 0;
+      if (++ty == p.tiles_y) { ty = 0; ++sample; }
+    }
+  }
+};
 
 template <int CIN, int NSPLIT>
 struct ConvFoldSmem {
@@ -83,7 +108,6 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int tiles_per_sample = p.tiles_x * p.tiles_y;
 
   if (warp == 0 && lane == 0) {
     if (smem_u32(smem_raw) & 1023u) {
@@ -126,74 +150,84 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           tma_load_2d(smem_u32(wsm + (pl * 3 + r) * L::kWBlockBytes), &tmW, wb, 0, (pl * 9 + r * 3) * 32);
       int slot = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-        const int sample = t / tiles_per_sample;
-        const int rem = t - sample * tiles_per_sample;
-        const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
-        const int cx = tx * kFoldValid - 1, cy = ty * 4 - 1;
+      FoldTileWalk w;
+      for (w.init(p); w.valid(); w.next(p)) {
+        const int cx = w.tx * kFoldValid - 1, cy = w.ty * 4 - 1;
         for (int pl = 0; pl < L::kPlanes; ++pl) {
           mbar_wait(smem_u32(&empty_bar[slot]), phase ^ 1);
           const uint32_t fb = smem_u32(&full_bar[slot]);
           mbar_arrive_expect_tx(fb, L::kSlotBytes);
           tma_load_5d(smem_u32(ring + (size_t)slot * L::kSlotBytes), &tmA, fb, p.a_c0 + pl * p.a_lo_off, cx, 0, cy,
-                      sample);
+                      w.sample);
           if (++slot == slots) { slot = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== UMMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, kFoldN);
-      mbar_wait(smem_u32(w_bar), 0);
+    // The whole warp walks the loop (uniform control flow keeps the descriptor arithmetic on the
+    // uniform datapath); one elected lane issues the MMAs and commits.
+    constexpr uint32_t idesc = umma_idesc_bf16(128, kFoldN);
+    constexpr uint32_t kDescHi = umma_smem_desc_hi(kRowBytes);
+    mbar_wait(smem_u32(w_bar), 0);
+    tc_fence_after();
+    const uint32_t w_hi = umma_smem_desc_lo(smem_u32(wsm));
+    const uint32_t w_lo = w_hi + ((3 * L::kWBlockBytes) >> 4);
+    const uint32_t ring_lo = umma_smem_desc_lo(smem_u32(ring));
+    int slot = 0;
+    uint32_t phase = 0;
+    uint32_t acc = 0, acc_phase = 0;
+    const int n_my = (int)((long long)p.total_tiles * (blockIdx.x + 1) / gridDim.x) -
+                     (int)((long long)p.total_tiles * blockIdx.x / gridDim.x);
+    for (int i = 0; i < n_my; ++i) {
+      mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);
+      mbar_wait(smem_u32(&full_bar[slot]), phase);
       tc_fence_after();
-      const uint32_t w_hi = smem_u32(wsm);
-      const uint32_t w_lo = w_hi + 3 * L::kWBlockBytes;
-      int slot = 0;
-      uint32_t phase = 0;
-      uint32_t acc = 0, acc_phase = 0;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-        mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * kFoldAccStride;
-        // hi plane of the activations: a_hi * w_hi (+ a_hi * w_lo)
-        mbar_wait(smem_u32(&full_bar[slot]), phase);
-        tc_fence_after();
-        {
-          const uint32_t a = smem_u32(ring + (size_t)slot * L::kSlotBytes);
+      const uint32_t d_tmem = tmem_base + acc * kFoldAccStride;
+      // hi plane of the activations: a_hi * w_hi (+ a_hi * w_lo)
+      {
+        const uint32_t a = ring_lo + (uint32_t)slot * (L::kSlotBytes >> 4);
+        if (elect_one()) {
 #pragma unroll
           for (int r = 0; r < 3; ++r) {
+            if (p.dbg & 1) break;
 #pragma unroll
             for (int k = 0; k < CIN / 16; ++k) {
-              const uint64_t da = umma_smem_desc(a + r * 32 * kRowBytes + k * 32, kRowBytes);
-              umma_bf16(d_tmem, da, umma_smem_desc(w_hi + r * L::kWBlockBytes + k * 32, kRowBytes), idesc,
+              const uint32_t ao = a + ((r * 32 * kRowBytes + k * 32) >> 4);
+              const uint32_t wo = (r * L::kWBlockBytes + k * 32) >> 4;
+              umma_bf16(d_tmem, make_desc(ao, kDescHi), make_desc(w_hi + wo, kDescHi), idesc,
                         (r > 0 || k > 0) ? 1u : 0u);
-              if (NSPLIT == 3)
-                umma_bf16(d_tmem, da, umma_smem_desc(w_lo + r * L::kWBlockBytes + k * 32, kRowBytes), idesc, 1u);
+              if (NSPLIT == 3) umma_bf16(d_tmem, make_desc(ao, kDescHi), make_desc(w_lo + wo, kDescHi), idesc, 1u);
             }
           }
+          umma_commit(smem_u32(&empty_bar[slot]));
+          if (NSPLIT == 1) umma_commit(smem_u32(&tfull_bar[acc]));
         }
-        umma_commit(smem_u32(&empty_bar[slot]));
-        if (++slot == slots) { slot = 0; phase ^= 1; }
-        if (NSPLIT == 3) {
-          // lo plane: a_lo * w_hi
-          mbar_wait(smem_u32(&full_bar[slot]), phase);
-          tc_fence_after();
-          const uint32_t a = smem_u32(ring + (size_t)slot * L::kSlotBytes);
+        __syncwarp();
+      }
+      if (++slot == slots) { slot = 0; phase ^= 1; }
+      if (NSPLIT == 3) {
+        // lo plane: a_lo * w_hi
+        mbar_wait(smem_u32(&full_bar[slot]), phase);
+        tc_fence_after();
+        const uint32_t a = ring_lo + (uint32_t)slot * (L::kSlotBytes >> 4);
+        if (elect_one()) {
 #pragma unroll
           for (int r = 0; r < 3; ++r) {
+            if (p.dbg & 1) break;
 #pragma unroll
             for (int k = 0; k < CIN / 16; ++k)
-              umma_bf16(d_tmem, umma_smem_desc(a + r * 32 * kRowBytes + k * 32, kRowBytes),
-                        umma_smem_desc(w_hi + r * L::kWBlockBytes + k * 32, kRowBytes), idesc, 1u);
+              umma_bf16(d_tmem, make_desc(a + ((r * 32 * kRowBytes + k * 32) >> 4), kDescHi),
+                        make_desc(w_hi + ((r * L::kWBlockBytes + k * 32) >> 4), kDescHi), idesc, 1u);
           }
           umma_commit(smem_u32(&empty_bar[slot]));
-          if (++slot == slots) { slot = 0; phase ^= 1; }
+          umma_commit(smem_u32(&tfull_bar[acc]));
         }
-        umma_commit(smem_u32(&tfull_bar[acc]));
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1;
+        __syncwarp();
+        if (++slot == slots) { slot = 0; phase ^= 1; }
       }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
     }
   } else {
     // ===================== epilogue: two groups of 4 warps, alternating tiles =====================
@@ -206,12 +240,11 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     float* eha = eh + group * 32;
     int prev_sample = -1;
     int it = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+    FoldTileWalk w;
+    for (w.init(p); w.valid(); w.next(p), ++it) {
       if ((it & 1) != group) continue;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
-      const int sample = t / tiles_per_sample;
-      const int rem = t - sample * tiles_per_sample;
-      const int ty = rem / p.tiles_x, tx = rem - ty * p.tiles_x;
+      const int sample = w.sample, ty = w.ty, tx = w.tx;
       if (sample != prev_sample) {  // uniform across the group
         prev_sample = sample;
         if (group == 0) asm volatile("bar.sync 1, 128;" ::: "memory");  // previous tile's table reads are done
@@ -227,8 +260,14 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       mbar_wait(smem_u32(&tfull_bar[acc]), acc_phase);
       tc_fence_after();
+      if (p.dbg & 2) {
+        tc_fence_before();
+        __syncwarp();
+        if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
+        continue;
+      }
       // the staging rows must no longer be read by this warp's previous TMA store
-      if (lane == 0) tma_store_wait_read<0>();
+      if (elect_one()) tma_store_wait_read<0>();
       __syncwarp();
       const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kFoldAccStride;
       const int row = lane - 1;  // staging row of this lane's output pixel (lanes 1..30)
@@ -242,7 +281,7 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (h == 1) {  // accumulator fully read
           tc_fence_before();
           __syncwarp();
-          if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+          if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
         }
         uint32_t hi[8], lo[8];
 #pragma unroll
@@ -284,14 +323,14 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
-        const int ox = tx * kFoldValid, oy = ty * 4 + q;
+      const int ox = tx * kFoldValid, oy = ty * 4 + q;
+      if (!(p.dbg & 4) && elect_one()) {
         tma_store_5d(&tmO, smem_u32(st_hi), p.out_hi_off, ox, 0, oy, sample);
         if (NSPLIT == 3) tma_store_5d(&tmO, smem_u32(st_lo), p.out_lo_off, ox, 0, oy, sample);
         tma_store_commit();
       }
     }
-    if (lane == 0) tma_store_wait_all();
+    if (elect_one()) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();

@@ -168,39 +168,44 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
   } else if (warp == 1) {
     // ===================== UMMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N);
-      int stage = 0;
-      uint32_t phase = 0;
-      uint32_t acc = 0, acc_phase = 0;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-        mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);  // epilogue has drained this accumulator
+    // The whole warp walks the loop (uniform control flow keeps the descriptor arithmetic on the
+    // uniform datapath); one elected lane issues the MMAs and commits.
+    constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N);
+    constexpr uint32_t kDescHi = umma_smem_desc_hi(kRowBytes);
+    const uint32_t ring_lo = umma_smem_desc_lo(smem_u32(smem));
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t acc = 0, acc_phase = 0;
+    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+      mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);  // epilogue has drained this accumulator
+      tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(smem_u32(&full_bar[stage]), phase);
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(smem_u32(&full_bar[stage]), phase);
-          tc_fence_after();
-          const uint32_t a_hi = smem_u32(smem + (size_t)stage * L::kStageBytes);
-          const uint32_t a_lo = a_hi + L::kABytes;
-          const uint32_t b_hi = a_hi + L::kPlanes * L::kABytes;
-          const uint32_t b_lo = b_hi + L::kBBytes;
+        const uint32_t a_hi = ring_lo + (uint32_t)stage * (L::kStageBytes >> 4);
+        const uint32_t a_lo = a_hi + (L::kABytes >> 4);
+        const uint32_t b_hi = a_hi + ((L::kPlanes * L::kABytes) >> 4);
+        const uint32_t b_lo = b_hi + (L::kBBytes >> 4);
+        if (elect_one()) {
 #pragma unroll
           for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = umma_smem_desc(a_hi + k * 32, kRowBytes);
-            const uint64_t db = umma_smem_desc(b_hi + k * 32, kRowBytes);
+            const uint64_t da = make_desc(a_hi + 2 * k, kDescHi);
+            const uint64_t db = make_desc(b_hi + 2 * k, kDescHi);
             umma_bf16(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
             if (NSPLIT == 3) {
-              umma_bf16(d_tmem, da, umma_smem_desc(b_lo + k * 32, kRowBytes), idesc, 1u);
-              umma_bf16(d_tmem, umma_smem_desc(a_lo + k * 32, kRowBytes), db, idesc, 1u);
+              umma_bf16(d_tmem, da, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
+              umma_bf16(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
             }
           }
           umma_commit(smem_u32(&empty_bar[stage]));  // frees the smem slot when the MMAs retire
-          if (++stage == stages) { stage = 0; phase ^= 1; }
+          if (kb == num_kb - 1) umma_commit(smem_u32(&tfull_bar[acc]));  // accumulator complete
         }
-        umma_commit(smem_u32(&tfull_bar[acc]));  // accumulator complete
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1;
+        __syncwarp();
+        if (++stage == stages) { stage = 0; phase ^= 1; }
       }
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
     }
   } else {
     // ===================== epilogue: two groups of 4 warps =====================
@@ -234,7 +239,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll 1
       for (int c0 = 0; c0 < BLOCK_N; c0 += CW) {
         // staging buffer `obuf` must no longer be read by an earlier TMA store of this warp
-        if (lane == 0) {
+        if (elect_one()) {
           if (nbuf == 1) tma_store_wait_read<0>(); else tma_store_wait_read<1>();
         }
         __syncwarp();
@@ -248,7 +253,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (c0 + CW >= BLOCK_N && h == CW / 32 - 1) {  // last read of this accumulator: hand it back
             tc_fence_before();
             __syncwarp();
-            if (lane == 0) mbar_arrive(smem_u32(&tempty_bar[acc]));
+            if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
           }
           uint32_t hi[16], lo[16];
 #pragma unroll
@@ -283,14 +288,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         fence_proxy_async_smem();
         __syncwarp();
-        if (lane == 0) {
-          int cbase = tc.n0 + c0, cx = tc.x0, cp = 0, cy = tc.y0 + 2 * q, coff = 0;
-          if (p.shuffle) {  // stride-2 view of the output: (2*pitch, W/2, 2, H/2, S)
-            const int quad = cbase / p.cout;
-            cbase -= quad * p.cout;
-            coff = (quad & 1) * (int)p.out_pitch;
-            cp = quad >> 1;
-          }
+        int cbase = tc.n0 + c0, cx = tc.x0, cp = 0, cy = tc.y0 + 2 * q, coff = 0;
+        if (p.shuffle) {  // stride-2 view of the output: (2*pitch, W/2, 2, H/2, S)
+          const int quad = cbase / p.cout;
+          cbase -= quad * p.cout;
+          coff = (quad & 1) * (int)p.out_pitch;
+          cp = quad >> 1;
+        }
+        if (elect_one()) {
           tma_store_5d(&tmO, smem_u32(sub_hi), coff + p.out_hi_off + cbase, cx, cp, cy, tc.sample);
           if (NSPLIT == 3) tma_store_5d(&tmO, smem_u32(sub_lo), coff + p.out_lo_off + cbase, cx, cp, cy, tc.sample);
           tma_store_commit();
@@ -298,7 +303,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (++obuf == nbuf) obuf = 0;
       }
     }
-    if (lane == 0) tma_store_wait_all();  // all output tiles of this warp have landed
+    if (elect_one()) tma_store_wait_all();  // all output tiles of this warp have landed
   }
   tc_fence_before();
   __syncthreads();
