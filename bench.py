@@ -207,7 +207,8 @@ def run_b200(args):
     lo = rank * n  # global positions of this rank's shard (weak scaling: shards are disjoint pools)
 
     def step_resident():
-        scores = eng.scores(pool_dev, "entropy", T=T_REPEATS, drop_p=DROP_P, seed=MC_SEED, base_pos=lo)
+        # MC-dropout masks are keyed by the position inside the rank's own pool (as in the selector path below)
+        scores = eng.scores(pool_dev, "entropy", T=T_REPEATS, drop_p=DROP_P, seed=MC_SEED, base_pos=0)
         vals, pos = eng.topk(scores, BUDGET, base_pos=lo)
         if world > 1:
             vals, pos = D.global_topk(vals, pos, BUDGET)
