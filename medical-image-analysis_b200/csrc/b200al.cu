@@ -80,10 +80,13 @@ struct b200al_ctx {
   std::vector<Layer> layers;  // 21 tensor-core layers in forward order (first conv and head are separate)
   // first conv + head
   float *first_w = nullptr, *first_bias = nullptr, *first_scale = nullptr, *first_shift = nullptr;
+  FirstConvConsts first_consts;  // host copy of the folded first-conv constants (passed as a kernel parameter)
   float *head_w = nullptr, *head_b = nullptr;
   float* ones = nullptr;   // [512] ones  (convT scale)
   float* zeros = nullptr;  // [512] zeros (convT shift)
   float* mask = nullptr;   // [max_samples][2944]
+  float* logits_buf = nullptr;  // [max_samples][K][H][W] when the head is fused into the last block
+  bool fuse_head = false;
   double* partial = nullptr;
   int partial_blocks = 0;
   float slope = 0.01f;
@@ -252,14 +255,23 @@ int conv_smem_bytes(int bn, int bk, int nsplit, int stages, int cw, int nbufs_to
 }
 
 typedef void (*FoldKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const ConvFoldParams, const int);
-FoldKernelFn pick_fold_kernel(int cin, int nsplit) {
-  if (cin == 32) return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<32, 3> : (FoldKernelFn)conv_fold_kernel<32, 1>;
-  if (cin == 64) return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<64, 3> : (FoldKernelFn)conv_fold_kernel<64, 1>;
+FoldKernelFn pick_fold_kernel(int cin, int nsplit, int headk = 0) {
+  if (cin == 32) {
+    switch (headk) {
+      case 0: return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<32, 3, 0> : (FoldKernelFn)conv_fold_kernel<32, 1, 0>;
+      case 2: return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<32, 3, 2> : (FoldKernelFn)conv_fold_kernel<32, 1, 2>;
+      case 3: return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<32, 3, 3> : (FoldKernelFn)conv_fold_kernel<32, 1, 3>;
+      case 4: return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<32, 3, 4> : (FoldKernelFn)conv_fold_kernel<32, 1, 4>;
+    }
+    return nullptr;
+  }
+  if (cin == 64 && headk == 0)
+    return nsplit == 3 ? (FoldKernelFn)conv_fold_kernel<64, 3, 0> : (FoldKernelFn)conv_fold_kernel<64, 1, 0>;
   return nullptr;
 }
 int fold_smem_bytes(int cin, int nsplit, int slots) {
   const int planes = nsplit == 3 ? 2 : 1;
-  return planes * 3 * kFoldN * cin * 2 + slots * 6 * 32 * cin * 2 + 8 * planes * 2048 + 2048;
+  return planes * 3 * kFoldN * cin * 2 + slots * 6 * 32 * cin * 2 + 8 * planes * 2048 + 3072;
 }
 
 int env_int(const char* name, int dflt) {
@@ -395,10 +407,12 @@ int make_layer_maps(b200al_ctx* ctx, const Layer& L, const __nv_bfloat16* in, co
 }
 
 int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtensorMap& tmO, const ConvTcParams& p, int S,
-                cudaStream_t st) {
+                cudaStream_t st, float* head_logits = nullptr) {
   if (L.fold) {
-    FoldKernelFn ffn = pick_fold_kernel(L.cin, ctx->nsplit);
+    FoldKernelFn ffn = pick_fold_kernel(L.cin, ctx->nsplit, head_logits ? ctx->K : 0);
+    if (!ffn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no folded kernel for Cin=%d head K=%d", L.cin, ctx->K);
     ConvFoldParams f = L.fp;
+    f.head_w = ctx->head_w; f.head_b = ctx->head_b; f.logits = head_logits; f.H = ctx->H; f.W = ctx->W;
     f.scale = p.scale; f.bias = p.bias; f.shift = p.shift; f.mask = p.mask; f.slope = p.slope;
     f.total_tiles = S * f.tiles_x * f.tiles_y;
     dim3 fgrid((unsigned)(f.total_tiles < ctx->sm_count ? f.total_tiles : ctx->sm_count));
@@ -536,6 +550,12 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
       TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * 9 * L.cout, L.cin, L.cin, kFoldN));
       FoldKernelFn ffn = pick_fold_kernel(L.cin, ctx->nsplit);
       TRY_CU(cudaFuncSetAttribute(ffn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+      if (&L == &ctx->layers.back() && pick_fold_kernel(L.cin, ctx->nsplit, ctx->K) && env_int("B200AL_FUSE_HEAD", 1)) {
+        TRY_CU(cudaFuncSetAttribute(pick_fold_kernel(L.cin, ctx->nsplit, ctx->K),
+                                    cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+        TRY_RC(dev_alloc(ctx, &ctx->logits_buf, (size_t)max_samples * ctx->K * H * W));
+        ctx->fuse_head = true;
+      }
       if (env_int("B200AL_VERBOSE", 0))
         fprintf(stderr, "b200al plan: fold %d->%d slots=%d smem=%d\n", L.cin, L.cout, L.slots,
                 fold_smem_bytes(L.cin, ctx->nsplit, L.slots));
@@ -619,6 +639,10 @@ extern "C" int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, voi
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->first_bias, b0.d_conv_bias, 32 * sizeof(float), cudaMemcpyDeviceToDevice, st));
   fold_bn_kernel<<<1, 32, 0, st>>>(b0.d_bn_gamma, b0.d_bn_beta, b0.d_bn_mean, b0.d_bn_var, w->bn_eps, ctx->first_scale,
                                    ctx->first_shift, 32);
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->first_consts.w, ctx->first_w, sizeof(ctx->first_consts.w), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->first_consts.bias, ctx->first_bias, 32 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->first_consts.scale, ctx->first_scale, 32 * sizeof(float), cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->first_consts.shift, ctx->first_shift, 32 * sizeof(float), cudaMemcpyDeviceToHost, st));
   for (Layer& L : ctx->layers) {
     L.p.slope = L.kind == KIND_CONV3 ? ctx->slope : 1.0f;
     if (L.kind == KIND_CONV3) {
@@ -643,6 +667,7 @@ extern "C" int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, voi
                                 cudaMemcpyDeviceToDevice, st));
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->head_b, w->d_head_bias, (size_t)ctx->K * sizeof(float), cudaMemcpyDeviceToDevice, st));
   CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaStreamSynchronize(st));  // the host copy of the first-conv constants must have landed
   ctx->weights_loaded = true;
   return B200AL_OK;
 }
@@ -652,19 +677,20 @@ extern "C" int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, voi
 // ---------------------------------------------------------------------------
 namespace {
 
-int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, int S, int T, const float* mask, cudaStream_t st) {
-  dim3 grid((ctx->W + 255) / 256, ctx->H, S);
+// first conv over n images, each expanded to T samples (sample = image * T + t); mask nullable [n*T][2944]
+int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, int n, int T, const float* mask, cudaStream_t st) {
+  dim3 grid((ctx->W + 255) / 256, ctx->H, n);
   const ActBuf& ob = ctx->bufs[E0A];
+  const size_t smem = (size_t)T * 64 * sizeof(float);
+  if (smem > 48 * 1024) return set_err(ctx, B200AL_ERR_ARG, "T = %d too large", T);
   if (dtype == B200AL_U8)
-    conv_first_kernel<uint8_t><<<grid, 256, 0, st>>>((const uint8_t*)d_images, T, ctx->H, ctx->W, ctx->first_w,
-                                                    ctx->first_bias, ctx->first_scale, ctx->first_shift, mask,
-                                                    B200AL_MASK_CHANNELS, ctx->slope, ob.ptr, 2 * ob.c_total, 0,
-                                                    ob.c_total, ctx->nsplit == 3);
+    conv_first_kernel<uint8_t><<<grid, 256, smem, st>>>((const uint8_t*)d_images, T, ctx->H, ctx->W, ctx->first_consts,
+                                                       mask, B200AL_MASK_CHANNELS, ctx->slope, ob.ptr, 2 * ob.c_total,
+                                                       0, ob.c_total, ctx->nsplit == 3);
   else if (dtype == B200AL_F32)
-    conv_first_kernel<float><<<grid, 256, 0, st>>>((const float*)d_images, T, ctx->H, ctx->W, ctx->first_w,
-                                                  ctx->first_bias, ctx->first_scale, ctx->first_shift, mask,
-                                                  B200AL_MASK_CHANNELS, ctx->slope, ob.ptr, 2 * ob.c_total, 0,
-                                                  ob.c_total, ctx->nsplit == 3);
+    conv_first_kernel<float><<<grid, 256, smem, st>>>((const float*)d_images, T, ctx->H, ctx->W, ctx->first_consts, mask,
+                                                     B200AL_MASK_CHANNELS, ctx->slope, ob.ptr, 2 * ob.c_total, 0,
+                                                     ob.c_total, ctx->nsplit == 3);
   else
     return set_err(ctx, B200AL_ERR_ARG, "bad image dtype %d", dtype);
   ctx->launches++;
@@ -673,12 +699,13 @@ int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, int S, int 
 }
 
 // layers [0, n_layers) of ctx->layers on S samples; mask nullable [S][2944]
-int run_layers(b200al_ctx* ctx, int n_layers, int S, const float* mask, cudaStream_t st) {
+// head_logits non-null: the last layer applies the fused seg_output head and writes logits there
+int run_layers(b200al_ctx* ctx, int n_layers, int S, const float* mask, cudaStream_t st, float* head_logits = nullptr) {
   for (int i = 0; i < n_layers; ++i) {
     Layer& L = ctx->layers[i];
     ConvTcParams p = L.p;
     p.mask = (mask && L.kind == KIND_CONV3) ? mask + L.mask_off : nullptr;
-    int rc = launch_conv(ctx, L, L.tmA, L.tmO, p, S, st);
+    int rc = launch_conv(ctx, L, L.tmA, L.tmO, p, S, st, i == n_layers - 1 ? head_logits : nullptr);
     if (rc) return rc;
   }
   return 0;
@@ -748,13 +775,24 @@ extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int ima
   int rc = prepare_masks(ctx, n, T, drop_p, mc_seed, base_pos, d_drop_masks, &mask, st);
   if (rc) return rc;
   const int S = n * T;
-  if ((rc = run_first_conv(ctx, d_images, image_dtype, S, T, mask, st))) return rc;
-  if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st))) return rc;
+  if ((rc = run_first_conv(ctx, d_images, image_dtype, n, T, mask, st))) return rc;
+  int nblk = ctx->partial_blocks;
+  if (ctx->fuse_head) {
+    // last decoder block + seg_output fused: logits [S][K][HW] fp32, then the HBM-bound softmax/score reduction
+    float* lg = d_logits_out ? d_logits_out : ctx->logits_buf;
+    if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st, lg))) return rc;
+    const int HW = ctx->H * ctx->W;
+    if ((HW / 4 + 255) / 256 < nblk) nblk = (HW / 4 + 255) / 256;
+#define CALL_UNC(KK) launch_unc<KK>(lg, n, T, HW, mode, smooth, ctx->partial, nblk, st)
+    DISPATCH_K(ctx->K, CALL_UNC)
+#undef CALL_UNC
+  } else {
+    if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st))) return rc;
 #define CALL_HEAD(KK) launch_head<KK>(ctx, n, T, mode, smooth, d_logits_out, st)
-  DISPATCH_K(ctx->K, CALL_HEAD)
+    DISPATCH_K(ctx->K, CALL_HEAD)
 #undef CALL_HEAD
-  uncertainty_finalize_kernel<<<(n + 127) / 128, 128, 0, st>>>(ctx->partial, ctx->partial_blocks, ctx->H * ctx->W,
-                                                              d_scores_out, n);
+  }
+  uncertainty_finalize_kernel<<<(n + 127) / 128, 128, 0, st>>>(ctx->partial, nblk, ctx->H * ctx->W, d_scores_out, n);
   ctx->launches += 2;
   CUDA_TRY(ctx, cudaGetLastError());
   return B200AL_OK;

@@ -40,6 +40,11 @@ struct ConvFoldParams {
   int mask_stride;
   float slope;
   int out_hi_off, out_lo_off;
+  // fused 1x1 seg_output head (HEADK > 0): logits [S][HEADK][H][W] fp32 instead of the activation
+  const float* head_w;  // [HEADK][32]
+  const float* head_b;  // [HEADK]
+  float* logits;
+  int H, W;
   int dbg;  // timing experiments only (B200AL_FOLD_DBG): 1 = no MMAs, 2 = no epilogue math/stores, 4 = no TMA stores
 };
 
@@ -81,11 +86,14 @@ struct ConvFoldSmem {
   static constexpr int kSlotBytes = 6 * 32 * kRowBytes;          // one plane of one halo tile
   static constexpr int kStagePlaneBytes = 2048;                  // 30 px x 64 B, padded
   static constexpr int kStagingBytes = 8 * kPlanes * kStagePlaneBytes;
-  static constexpr int kTailBytes = 2048;                        // barriers, tmem ptr, affine tables
+  static constexpr int kTailBytes = 3072;                        // barriers, tmem ptr, affine + head tables
   static constexpr int bytes(int slots) { return kWBytes + slots * kSlotBytes + kStagingBytes + kTailBytes; }
 };
 
-template <int CIN, int NSPLIT>
+// HEADK > 0 (last decoder block only): the epilogue applies the UNet's 1x1 seg_output conv to the
+// 32 fp32 channel values it holds in registers and stores HEADK logits per pixel; the activation
+// itself is not written.
+template <int CIN, int NSPLIT, int HEADK>
 __global__ void __launch_bounds__(kFoldThreads)
 conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmW,
                  const __grid_constant__ CUtensorMap tmO, const ConvFoldParams p, const int slots) {
@@ -105,6 +113,7 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(w_bar + 1);
   float* es = reinterpret_cast<float*>(tail + 512);          // [2 groups][32]
   float* eh = es + 64;                                       // [2 groups][32]
+  float* hws = reinterpret_cast<float*>(tail + 1024);        // [HEADK][32] head weights, then [HEADK] bias
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -133,6 +142,10 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 2) {
     tmem_alloc(smem_u32(tmem_slot), kTmemCols);
     tmem_relinquish();
+  }
+  if (HEADK > 0 && warp >= 3) {
+    for (int i = threadIdx.x - 96; i < HEADK * 33; i += kFoldThreads - 96)
+      hws[i] = i < HEADK * 32 ? p.head_w[i] : p.head_b[i - HEADK * 32];
   }
   tc_fence_before();
   __syncthreads();
@@ -267,22 +280,30 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         continue;
       }
       // the staging rows must no longer be read by this warp's previous TMA store
-      if (elect_one()) tma_store_wait_read<0>();
-      __syncwarp();
+      if (HEADK == 0) {
+        if (elect_one()) tma_store_wait_read<0>();
+        __syncwarp();
+      }
+      float lg[HEADK > 0 ? HEADK : 1];
+#pragma unroll
+      for (int k = 0; k < HEADK; ++k) lg[k] = hws[HEADK * 32 + k];
       const uint32_t trow = tmem_base + ((uint32_t)(q * 32) << 16) + acc * kFoldAccStride;
       const int row = lane - 1;  // staging row of this lane's output pixel (lanes 1..30)
+      // pull the whole accumulator into registers and hand the TMEM stage back before the math
+      uint32_t dd[2][3][16];
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+        for (int s3 = 0; s3 < 3; ++s3) tmem_ld_32x32_x16(trow + s3 * 32 + h * 16, dd[h][s3]);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
 #pragma unroll
       for (int h = 0; h < 2; ++h) {  // 16 output channels per pass
-        uint32_t d0[16], d1[16], d2[16];
-        tmem_ld_32x32_x16(trow + h * 16, d0);
-        tmem_ld_32x32_x16(trow + 32 + h * 16, d1);
-        tmem_ld_32x32_x16(trow + 64 + h * 16, d2);
-        tmem_ld_wait();
-        if (h == 1) {  // accumulator fully read
-          tc_fence_before();
-          __syncwarp();
-          if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
-        }
+        const uint32_t(&d0)[16] = dd[h][0];
+        const uint32_t(&d1)[16] = dd[h][1];
+        const uint32_t(&d2)[16] = dd[h][2];
         uint32_t hi[8], lo[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
@@ -299,6 +320,14 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           float y1f = fmaf(a1, sc2.y, sh2.y);
           y0f = fmaxf(y0f, y0f * p.slope);
           y1f = fmaxf(y1f, y1f * p.slope);
+          if (HEADK > 0) {
+#pragma unroll
+            for (int k = 0; k < HEADK; ++k) {
+              const float2 w2 = *reinterpret_cast<const float2*>(hws + k * 32 + cc);
+              lg[k] = fmaf(y1f, w2.y, fmaf(y0f, w2.x, lg[k]));
+            }
+            continue;
+          }
           const __nv_bfloat162 h2 = __floats2bfloat162_rn(y0f, y1f);
           const uint32_t hb = *reinterpret_cast<const uint32_t*>(&h2);
           hi[j] = hb;
@@ -308,7 +337,7 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
           }
         }
-        if (lane >= 1 && lane <= kFoldValid) {
+        if (HEADK == 0 && lane >= 1 && lane <= kFoldValid) {
           // 64-byte rows, SWIZZLE_64B: 16-byte chunk c of row `row` lives at chunk (c ^ ((row >> 1) & 3))
 #pragma unroll
           for (int j = 0; j < 2; ++j) {
@@ -321,16 +350,25 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
+      const int ox = tx * kFoldValid, oy = ty * 4 + q;
+      if (HEADK > 0) {
+        const int x = ox + lane - 1;
+        if (lane >= 1 && lane <= kFoldValid && x < p.W) {
+          float* dst = p.logits + (((size_t)sample * HEADK) * p.H + oy) * p.W + x;
+#pragma unroll
+          for (int k = 0; k < HEADK; ++k) dst[(size_t)k * p.H * p.W] = lg[k];
+        }
+        continue;
+      }
       fence_proxy_async_smem();
       __syncwarp();
-      const int ox = tx * kFoldValid, oy = ty * 4 + q;
       if (!(p.dbg & 4) && elect_one()) {
         tma_store_5d(&tmO, smem_u32(st_hi), p.out_hi_off, ox, 0, oy, sample);
         if (NSPLIT == 3) tma_store_5d(&tmO, smem_u32(st_lo), p.out_lo_off, ox, 0, oy, sample);
         tma_store_commit();
       }
     }
-    if (elect_one()) tma_store_wait_all();
+    if (HEADK == 0 && elect_one()) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();

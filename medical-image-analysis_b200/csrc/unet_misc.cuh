@@ -69,28 +69,41 @@ __global__ void mc_mask_kernel(float* __restrict__ mask, int n_samples, int T, i
 }
 
 // First conv: 1 -> 32 channels, 3x3, pad 1, fp32 math on CUDA cores (K = 9).
-// One thread per output pixel, all 32 channels; sample s reads image s / T.
+// One thread per output pixel of one IMAGE: the 32 pre-activation sums are computed
+// once and reused by the T MC-dropout repeats (samples img*T .. img*T+T-1), which
+// differ only in the per-sample channel mask folded into the BN scale.  The filter
+// and the folded BN constants travel as a kernel parameter, so every FMA takes its
+// weight from the constant bank instead of a shared-memory load.
+struct FirstConvConsts {
+  float w[32 * 9];
+  float bias[32], scale[32], shift[32];
+};
+
 template <typename ImgT>
 __global__ void __launch_bounds__(256)
-conv_first_kernel(const ImgT* __restrict__ img, int T, int H, int W, const float* __restrict__ w /*[32][9]*/,
-                  const float* __restrict__ bias, const float* __restrict__ scale, const float* __restrict__ shift,
+conv_first_kernel(const ImgT* __restrict__ img, int T, int H, int W, const __grid_constant__ FirstConvConsts k,
                   const float* __restrict__ mask, int mask_stride, float slope, __nv_bfloat16* __restrict__ out,
                   int out_pitch, int hi_off, int lo_off, int write_lo) {
-  __shared__ float sw[32 * 9];
-  __shared__ float ses[32], seh[32];
-  const int s = blockIdx.z;
-  for (int i = threadIdx.x; i < 288; i += blockDim.x) sw[i] = w[i];
-  if (threadIdx.x < 32) {
-    float sc = scale[threadIdx.x];
-    if (mask) sc *= mask[(size_t)s * mask_stride + threadIdx.x];
-    ses[threadIdx.x] = sc;
-    seh[threadIdx.x] = bias[threadIdx.x] * sc + shift[threadIdx.x];
+  extern __shared__ float se[];  // [T][32] scale, then [T][32] shift
+  float* ses = se;
+  float* seh = se + T * 32;
+  const int im_idx = blockIdx.z;
+  for (int i = threadIdx.x; i < T * 32; i += blockDim.x) {
+    const int t = i >> 5, c = i & 31;
+    float sc = k.scale[c];
+    if (mask) sc *= mask[(size_t)(im_idx * T + t) * mask_stride + c];
+    ses[i] = sc;
+    seh[i] = k.bias[c] * sc + k.shift[c];
   }
   __syncthreads();
+  // every store instruction of a warp must cover contiguous bytes (a lane-strided 16-byte store costs
+  // one L1 wavefront per lane): the 32 pixels x 128 B of a warp are transposed through shared memory
+  __shared__ uint4 stg[8][32 * 8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
+  const int x0w = x - lane;
   const int y = blockIdx.y;
-  if (x >= W) return;
-  const ImgT* im = img + (size_t)(s / T) * H * W;
+  const ImgT* im = img + (size_t)im_idx * H * W;
   float v[9];
 #pragma unroll
   for (int r = 0; r < 3; ++r)
@@ -104,31 +117,49 @@ conv_first_kernel(const ImgT* __restrict__ img, int T, int H, int W, const float
       }
       v[r * 3 + c] = t;
     }
-  __nv_bfloat16* dst = out + ((size_t)((size_t)s * H + y) * W + x) * out_pitch;
-  uint32_t hi[16], lo[16];
+  float acc[32];
 #pragma unroll
-  for (int co = 0; co < 32; co += 2) {
-    float a0 = 0.f, a1 = 0.f;
+  for (int co = 0; co < 32; ++co) {
+    float a = 0.f;
 #pragma unroll
-    for (int k = 0; k < 9; ++k) {
-      a0 = fmaf(v[k], sw[co * 9 + k], a0);
-      a1 = fmaf(v[k], sw[(co + 1) * 9 + k], a1);
-    }
-    a0 = leaky(a0 * ses[co] + seh[co], slope);
-    a1 = leaky(a1 * ses[co + 1] + seh[co + 1], slope);
-    __nv_bfloat16 h0, l0, h1, l1;
-    split_bf16(a0, h0, l0);
-    split_bf16(a1, h1, l1);
-    hi[co / 2] = pack_bf16x2(h0, h1);
-    lo[co / 2] = pack_bf16x2(l0, l1);
+    for (int kk = 0; kk < 9; ++kk) a = fmaf(v[kk], k.w[co * 9 + kk], a);
+    acc[co] = a;
   }
-  uint4* dh = reinterpret_cast<uint4*>(dst + hi_off);
+  uint4* ws = stg[warp];
+  for (int t = 0; t < T; ++t) {
+    const float* sc = ses + t * 32;
+    const float* sh = seh + t * 32;
+    uint32_t hi[16], lo[16];
 #pragma unroll
-  for (int j = 0; j < 4; ++j) dh[j] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
-  if (write_lo) {
-    uint4* dl = reinterpret_cast<uint4*>(dst + lo_off);
+    for (int co = 0; co < 32; co += 2) {
+      const float2 s2 = *reinterpret_cast<const float2*>(sc + co);
+      const float2 h2 = *reinterpret_cast<const float2*>(sh + co);
+      const float a0 = leaky(acc[co] * s2.x + h2.x, slope);
+      const float a1 = leaky(acc[co + 1] * s2.y + h2.y, slope);
+      __nv_bfloat16 h0, l0, h1, l1;
+      split_bf16(a0, h0, l0);
+      split_bf16(a1, h1, l1);
+      hi[co / 2] = pack_bf16x2(h0, h1);
+      lo[co / 2] = pack_bf16x2(l0, l1);
+    }
+    __syncwarp();
 #pragma unroll
-    for (int j = 0; j < 4; ++j) dl[j] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+    for (int j = 0; j < 4; ++j) {
+      ws[lane * 8 + (j ^ (lane & 7))] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
+      ws[lane * 8 + ((4 + j) ^ (lane & 7))] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+    }
+    __syncwarp();
+    __nv_bfloat16* dstw = out + ((size_t)((size_t)(im_idx * T + t) * H + y) * W + x0w) * out_pitch;
+    const int c = lane & 7;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int px = i * 4 + (lane >> 3);
+      const uint4 val = ws[px * 8 + (c ^ (px & 7))];
+      if (x0w + px < W && (c < 4 || write_lo)) {
+        __nv_bfloat16* d = dstw + (size_t)px * out_pitch + (c < 4 ? hi_off + c * 8 : lo_off + (c - 4) * 8);
+        *reinterpret_cast<uint4*>(d) = val;
+      }
+    }
   }
 }
 
