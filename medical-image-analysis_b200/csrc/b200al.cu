@@ -55,6 +55,7 @@ struct Layer {
   int mask_off = 0;
   int bn = 0, bk = 0, stages = 0, ctas_per_sm = 1, cw = 32, nbuf = 1, ngroups = 2;
   __nv_bfloat16* wp = nullptr;  // packed weights [plane][tap][N][Cin]
+  __nv_bfloat16* wp2 = nullptr; // folded Cin=32 layers: [tap][N][hi 32 | lo 32]
   float *scale = nullptr, *bias = nullptr, *shift = nullptr;
   CUtensorMap tmA, tmB, tmO;
   ConvTcParams p;
@@ -271,7 +272,8 @@ FoldKernelFn pick_fold_kernel(int cin, int nsplit, int headk = 0) {
 }
 int fold_smem_bytes(int cin, int nsplit, int slots) {
   const int planes = nsplit == 3 ? 2 : 1;
-  return planes * 3 * kFoldN * cin * 2 + slots * 6 * 32 * cin * 2 + 8 * planes * 2048 + 3072;
+  const int row = cin == 32 ? 128 : cin * 2;  // Cin = 32: hi and lo planes share one 128-byte row
+  return (cin == 32 ? 1 : planes) * 3 * kFoldN * row + slots * 6 * 32 * row + 8 * planes * 2048 + 3072;
 }
 
 int env_int(const char* name, int dflt) {
@@ -349,8 +351,10 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
       p.a_dy[i] = (i == 0) ? -1 : 0;
     }
   }
-  L.fold = L.kind == KIND_CONV3 && L.stride == 1 && L.cout == 32 && (L.cin == 32 || L.cin == 64) &&
-           outH % 4 == 0 && env_int("B200AL_FOLD", 1) != 0;
+  // Cout = 64 runs as two launches of 32 output channels each (the resident weights of one half fit, all 64 do not)
+  L.fold = L.kind == KIND_CONV3 && L.stride == 1 && outH % 4 == 0 && env_int("B200AL_FOLD", 1) != 0 &&
+           ((L.cin == 32 && L.cout == 32 && ib.c_total == 32 && L.in.c_off == 0) ||
+            (L.cin == 64 && (L.cout == 32 || (L.cout == 64 && env_int("B200AL_FOLD64", 1)))));
   if (L.fold) {
     ConvFoldParams& f = L.fp;
     memset(&f, 0, sizeof(f));
@@ -396,7 +400,8 @@ int make_layer_maps(b200al_ctx* ctx, const Layer& L, const __nv_bfloat16* in, co
   int rc;
   if (L.fold) {
     // A: 6-row x 32-column halo box, all Cin channels of one plane; O: one image row of 30 pixels x 32 channels
-    if ((rc = make_tma_act(ctx, tmA, in, S, inH, inW, 2 * ib.c_total, 1, L.cin, 32, 6))) return rc;
+    //    (Cin = 32: both planes of the pixel in one 64-element row)
+    if ((rc = make_tma_act(ctx, tmA, in, S, inH, inW, 2 * ib.c_total, 1, 64, 32, 6))) return rc;
     return make_tma_act(ctx, tmO, out, S, outH, outW, 2 * ob.c_total, 1, 32, kFoldValid, 1);
   }
   if ((rc = make_tma_act(ctx, tmA, in, S, inH, inW, 2 * ib.c_total, L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw,
@@ -419,10 +424,18 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
     const int fsmem = fold_smem_bytes(L.cin, ctx->nsplit, L.slots);
     const bool ft = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
     if (ft) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
-    ffn<<<fgrid, kFoldThreads, fsmem, st>>>(tmA, L.tmB, tmO, f, L.slots);
+    f.w_cout_total = L.cout;
+    for (int co0 = 0; co0 < L.cout; co0 += 32) {
+      ConvFoldParams g = f;
+      g.w_co0 = co0;
+      g.scale += co0; g.bias += co0; g.shift += co0;
+      if (g.mask) g.mask += co0;
+      g.out_hi_off += co0; g.out_lo_off += co0;
+      ffn<<<fgrid, kFoldThreads, fsmem, st>>>(tmA, L.tmB, tmO, g, L.slots);
+      ctx->launches++;
+      ctx->conv_launches++;
+    }
     if (ft) cudaEventRecord(ctx->ev[ctx->ev_used++], st);
-    ctx->launches++;
-    ctx->conv_launches++;
     CUDA_TRY(ctx, cudaGetLastError());
     return 0;
   }
@@ -547,7 +560,12 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
     TRY_RC(make_layer_maps(ctx, L, ctx->bufs[L.in.buf].ptr, ctx->bufs[L.out.buf].ptr, max_samples, &L.tmA, &L.tmO));
     if (L.fold) {
       // weights: rows [2 planes][9 taps][32], box = the three column taps of one filter row (96 rows) x Cin
-      TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * 9 * L.cout, L.cin, L.cin, kFoldN));
+      if (L.cin == 32) {
+        TRY_RC(dev_alloc(ctx, &L.wp2, (size_t)9 * L.cout * 64));
+        TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp2, 9 * L.cout, 64, 64, kFoldN));
+      } else {
+        TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * 9 * L.cout, L.cin, L.cin, 32));
+      }
       FoldKernelFn ffn = pick_fold_kernel(L.cin, ctx->nsplit);
       TRY_CU(cudaFuncSetAttribute(ffn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
       if (&L == &ctx->layers.back() && pick_fold_kernel(L.cin, ctx->nsplit, ctx->K) && env_int("B200AL_FUSE_HEAD", 1)) {
@@ -650,6 +668,7 @@ extern "C" int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, voi
       if (!b.d_conv_weight || !b.d_conv_bias || !b.d_bn_gamma || !b.d_bn_beta || !b.d_bn_mean || !b.d_bn_var)
         return set_err(ctx, B200AL_ERR_ARG, "NULL weight pointer in block %d", L.block);
       pack_conv3x3_kernel<<<256, 256, 0, st>>>(b.d_conv_weight, L.wp, L.cout, L.cin);
+      if (L.wp2) pack_conv3x3_rowpair_kernel<<<64, 256, 0, st>>>(b.d_conv_weight, L.wp2, L.cout);
       CUDA_TRY(ctx, cudaMemcpyAsync(L.bias, b.d_conv_bias, L.cout * sizeof(float), cudaMemcpyDeviceToDevice, st));
       fold_bn_kernel<<<(L.cout + 127) / 128, 128, 0, st>>>(b.d_bn_gamma, b.d_bn_beta, b.d_bn_mean, b.d_bn_var,
                                                           w->bn_eps, L.scale, L.shift, L.cout);

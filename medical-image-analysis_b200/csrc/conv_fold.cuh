@@ -45,6 +45,8 @@ struct ConvFoldParams {
   const float* head_b;  // [HEADK]
   float* logits;
   int H, W;
+  int w_cout_total;  // output channels of the whole layer (row stride between filter taps in the packed weights)
+  int w_co0;         // first output channel of the 32 this launch computes
   int dbg;  // timing experiments only (B200AL_FOLD_DBG): 1 = no MMAs, 2 = no epilogue math/stores, 4 = no TMA stores
 };
 
@@ -77,13 +79,18 @@ struct FoldTileWalk {
   }
 };
 
+// CIN == 32 ("packed"): the hi and lo planes of a 32-channel pixel are adjacent in memory, so one
+// 128-byte SWIZZLE_128B row carries both (hi in bytes 0-63, lo in 64-127) and the weights are packed
+// the same way; the tensor core fetches 128-byte rows noticeably faster than 64-byte ones.
+// CIN == 64: one 128-byte row per plane, the planes travel in separate ring slots.
 template <int CIN, int NSPLIT>
 struct ConvFoldSmem {
+  static constexpr bool kPacked = (CIN == 32);
   static constexpr int kPlanes = (NSPLIT == 3) ? 2 : 1;
-  static constexpr int kRowBytes = CIN * 2;
-  static constexpr int kWBlockBytes = kFoldN * kRowBytes;        // one (plane, r) weight block
-  static constexpr int kWBytes = kPlanes * 3 * kWBlockBytes;
-  static constexpr int kSlotBytes = 6 * 32 * kRowBytes;          // one plane of one halo tile
+  static constexpr int kRowBytes = kPacked ? 128 : CIN * 2;
+  static constexpr int kWBlockBytes = kFoldN * kRowBytes;        // one filter row r (packed: both planes)
+  static constexpr int kWBytes = (kPacked ? 1 : kPlanes) * 3 * kWBlockBytes;
+  static constexpr int kSlotBytes = 6 * 32 * kRowBytes;          // one halo tile (packed) / one plane of it
   static constexpr int kStagePlaneBytes = 2048;                  // 30 px x 64 B, padded
   static constexpr int kStagingBytes = 8 * kPlanes * kStagePlaneBytes;
   static constexpr int kTailBytes = 3072;                        // barriers, tmem ptr, affine + head tables
@@ -155,18 +162,24 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (lane == 0) {
-      // resident weights: [plane][r] blocks of 96 rows (s, co) x CIN
+      // resident weights: blocks of 96 rows (s, co), one per filter row r (and per plane unless packed)
       const uint32_t wb = smem_u32(w_bar);
       mbar_arrive_expect_tx(wb, L::kWBytes);
-      for (int pl = 0; pl < L::kPlanes; ++pl)
-        for (int r = 0; r < 3; ++r)
-          tma_load_2d(smem_u32(wsm + (pl * 3 + r) * L::kWBlockBytes), &tmW, wb, 0, (pl * 9 + r * 3) * 32);
+      if (L::kPacked) {
+        for (int r = 0; r < 3; ++r) tma_load_2d(smem_u32(wsm + r * L::kWBlockBytes), &tmW, wb, 0, r * 3 * 32);
+      } else {
+        for (int pl = 0; pl < L::kPlanes; ++pl)
+          for (int r = 0; r < 3; ++r)
+            for (int s3 = 0; s3 < 3; ++s3)  // 32 of the layer's output channels per column tap
+              tma_load_2d(smem_u32(wsm + (pl * 3 + r) * L::kWBlockBytes + s3 * 32 * kRowBytes), &tmW, wb, 0,
+                          (pl * 9 + r * 3 + s3) * p.w_cout_total + p.w_co0);
+      }
       int slot = 0;
       uint32_t phase = 0;
       FoldTileWalk w;
       for (w.init(p); w.valid(); w.next(p)) {
         const int cx = w.tx * kFoldValid - 1, cy = w.ty * 4 - 1;
-        for (int pl = 0; pl < L::kPlanes; ++pl) {
+        for (int pl = 0; pl < (L::kPacked ? 1 : L::kPlanes); ++pl) {
           mbar_wait(smem_u32(&empty_bar[slot]), phase ^ 1);
           const uint32_t fb = smem_u32(&full_bar[slot]);
           mbar_arrive_expect_tx(fb, L::kSlotBytes);
@@ -197,6 +210,32 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       mbar_wait(smem_u32(&full_bar[slot]), phase);
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * kFoldAccStride;
+      if (L::kPacked) {
+        const uint32_t a = ring_lo + (uint32_t)slot * (L::kSlotBytes >> 4);
+        if (elect_one()) {
+#pragma unroll
+          for (int r = 0; r < 3; ++r) {
+            if (p.dbg & 1) break;
+#pragma unroll
+            for (int k = 0; k < 2; ++k) {
+              const uint32_t ah = a + ((r * 32 * kRowBytes + k * 32) >> 4), al = ah + 4;   // lo plane: +64 bytes
+              const uint32_t wh = w_hi + ((r * L::kWBlockBytes + k * 32) >> 4), wl = wh + 4;
+              umma_bf16(d_tmem, make_desc(ah, kDescHi), make_desc(wh, kDescHi), idesc, (r > 0 || k > 0) ? 1u : 0u);
+              if (NSPLIT == 3) {
+                umma_bf16(d_tmem, make_desc(ah, kDescHi), make_desc(wl, kDescHi), idesc, 1u);
+                umma_bf16(d_tmem, make_desc(al, kDescHi), make_desc(wh, kDescHi), idesc, 1u);
+              }
+            }
+          }
+          umma_commit(smem_u32(&empty_bar[slot]));
+          umma_commit(smem_u32(&tfull_bar[acc]));
+        }
+        __syncwarp();
+        if (++slot == slots) { slot = 0; phase ^= 1; }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+        continue;
+      }
       // hi plane of the activations: a_hi * w_hi (+ a_hi * w_lo)
       {
         const uint32_t a = ring_lo + (uint32_t)slot * (L::kSlotBytes >> 4);

@@ -23,6 +23,22 @@ __global__ void pack_conv3x3_kernel(const float* __restrict__ w, __nv_bfloat16* 
   }
 }
 
+// Conv2d weight [Cout][32][3][3] fp32 -> [tap][Cout][hi 32 | lo 32] bf16: 128-byte rows for the
+// packed variant of the column-folded kernel (conv_fold.cuh).
+__global__ void pack_conv3x3_rowpair_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wp, int cout) {
+  const int total = cout * 32 * 9;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int tap = i % 9;
+    const int ci = (i / 9) % 32;
+    const int co = i / (9 * 32);
+    __nv_bfloat16 hi, lo;
+    split_bf16(w[i], hi, lo);
+    const size_t o = ((size_t)tap * cout + co) * 64 + ci;
+    wp[o] = hi;
+    wp[o + 32] = lo;
+  }
+}
+
 // ConvTranspose2d weight [Cin][Cout][2][2] -> packed [plane][quad*Cout + co][Cin], quad = dy*2+dx.
 __global__ void pack_convT_kernel(const float* __restrict__ w, __nv_bfloat16* __restrict__ wp, int cin, int cout) {
   const int total = cin * cout * 4;
