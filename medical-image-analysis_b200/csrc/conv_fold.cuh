@@ -47,7 +47,7 @@ struct ConvFoldParams {
   int H, W;
   int w_cout_total;  // output channels of the whole layer (row stride between filter taps in the packed weights)
   int w_co0;         // first output channel of the 32 this launch computes
-  int dbg;  // timing experiments only (B200AL_FOLD_DBG): 1 = no MMAs, 2 = no epilogue math/stores, 4 = no TMA stores
+  int dbg;  // timing experiments only (B200AL_FOLD_DBG): 1 = no MMAs, 2 = no epilogue math/stores, 4 = no TMA stores, 8 = no TMA loads
 };
 
 constexpr int kFoldThreads = 320;   // TMA warp, MMA warp, 2 epilogue groups of 4 warps
@@ -182,9 +182,13 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int pl = 0; pl < (L::kPacked ? 1 : L::kPlanes); ++pl) {
           mbar_wait(smem_u32(&empty_bar[slot]), phase ^ 1);
           const uint32_t fb = smem_u32(&full_bar[slot]);
-          mbar_arrive_expect_tx(fb, L::kSlotBytes);
-          tma_load_5d(smem_u32(ring + (size_t)slot * L::kSlotBytes), &tmA, fb, p.a_c0 + pl * p.a_lo_off, cx, 0, cy,
-                      w.sample);
+          if (p.dbg & 8) {  // timing experiment: no activation loads at all
+            mbar_arrive(fb);
+          } else {
+            mbar_arrive_expect_tx(fb, L::kSlotBytes);
+            tma_load_5d(smem_u32(ring + (size_t)slot * L::kSlotBytes), &tmA, fb, p.a_c0 + pl * p.a_lo_off, cx, 0, cy,
+                        w.sample);
+          }
           if (++slot == slots) { slot = 0; phase ^= 1; }
         }
       }
