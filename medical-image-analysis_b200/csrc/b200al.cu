@@ -445,11 +445,30 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
   q.n_tiles = p.n_total / L.bn;
   q.total_tiles = S * p.tiles_x * p.tiles_y * q.n_tiles;
   const int resident = ctx->sm_count * L.ctas_per_sm;
-  dim3 grid((unsigned)(q.total_tiles < resident ? q.total_tiles : resident));
+  // CTA pairs with multicast weight tiles: pixel tiles come in pairs, one CTA per SM
+  const int m_tiles = S * p.tiles_x * p.tiles_y;
+  q.cluster = (L.ctas_per_sm == 1 && m_tiles % 2 == 0 && q.total_tiles >= 4 && env_int("B200AL_CLUSTER", 1)) ? 1 : 0;
+  unsigned nblk = (unsigned)(q.total_tiles < resident ? q.total_tiles : resident);
+  if (q.cluster) nblk &= ~1u;
   const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups);
   const bool t = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
   if (t) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
-  fn<<<grid, kConvThreads, smem, st>>>(tmA, L.tmB, tmO, q, L.stages, L.nbuf, L.ngroups);
+  {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(nblk);
+    cfg.blockDim = dim3(kConvThreads);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = q.cluster ? 2 : 1;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    CUDA_TRY(ctx, cudaLaunchKernelEx(&cfg, fn, tmA, L.tmB, tmO, (const ConvTcParams)q, (const int)L.stages, (const int)L.nbuf,
+                                     (const int)L.ngroups));
+  }
   if (t) cudaEventRecord(ctx->ev[ctx->ev_used++], st);
   ctx->launches++;
   ctx->conv_launches++;
@@ -580,7 +599,8 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
       continue;
     }
     // rows: conv [2 planes][9 taps][Cout]; convT [2 planes][1][4*Cout]
-    TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn));
+    // (boxes of BN/2 rows: a weight tile is fetched as two halves, see conv_tc.cuh)
+    TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn / 2));
     ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw);
     if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d CW=%d", L.bn, L.bk, L.cw); b200al_ctx_destroy(ctx); return rc; }
     const int smem_l = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups);

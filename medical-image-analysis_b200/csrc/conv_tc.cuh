@@ -51,6 +51,9 @@ struct ConvTcParams {
   int shuffle;  // 1: transposed conv, column n -> (quad=n/cout, co=n%cout), pixel (2y+quad/2, 2x+quad%2)
   int cout;     // channels per quad (== n_total when !shuffle)
   int write_lo;
+  // 1: launched as clusters of 2 CTAs that work on two adjacent pixel tiles of the same n-tile; each CTA
+  // fetches half of every weight tile and multicasts it to both (halves the L2->SM weight traffic)
+  int cluster;
 };
 
 constexpr int kConvThreads = 320;  // TMA warp + MMA warp + 2 epilogue groups of 4 warps
@@ -70,18 +73,30 @@ struct ConvTcSmem {
 struct TileCoord {
   int sample, x0, y0, n0;
 };
-__device__ __forceinline__ TileCoord decode_tile(const ConvTcParams& p, int t, int block_n) {
-  TileCoord c;
-  const int nt = t % p.n_tiles;
-  int m = t / p.n_tiles;
+// i-th tile of this CTA.  Plain launch: tiles blockIdx.x, +gridDim.x, ... with the n-tile fastest.
+// Cluster launch: cluster c walks tile PAIRS c, +nclusters, ...; a pair is two consecutive pixel tiles
+// of one n-tile, CTA rank r takes the r-th.
+__device__ __forceinline__ bool get_tile(const ConvTcParams& p, int i, int block_n, uint32_t rank, TileCoord* c) {
+  int nt, m;
+  if (p.cluster) {
+    const int pair = (int)(blockIdx.x >> 1) + i * (int)(gridDim.x >> 1);
+    if (pair >= (p.total_tiles >> 1)) return false;
+    nt = pair % p.n_tiles;
+    m = (pair / p.n_tiles) * 2 + (int)rank;
+  } else {
+    const int t = (int)blockIdx.x + i * (int)gridDim.x;
+    if (t >= p.total_tiles) return false;
+    nt = t % p.n_tiles;
+    m = t / p.n_tiles;
+  }
   const int tiles_per_sample = p.tiles_x * p.tiles_y;
-  c.sample = m / tiles_per_sample;
-  m -= c.sample * tiles_per_sample;
+  c->sample = m / tiles_per_sample;
+  m -= c->sample * tiles_per_sample;
   const int ty = m / p.tiles_x;
-  c.x0 = (m - ty * p.tiles_x) * p.tw;
-  c.y0 = ty * p.th;
-  c.n0 = nt * block_n;
-  return c;
+  c->x0 = (m - ty * p.tiles_x) * p.tw;
+  c->y0 = ty * p.th;
+  c->n0 = nt * block_n;
+  return true;
 }
 
 template <int BLOCK_N, int BK, int NSPLIT, int CW>
@@ -121,7 +136,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < stages; ++i) {
       mbar_init(smem_u32(&full_bar[i]), 1);
-      mbar_init(smem_u32(&empty_bar[i]), 1);
+      mbar_init(smem_u32(&empty_bar[i]), p.cluster ? 2 : 1);  // cluster: released by both CTAs' MMA warps
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&tfull_bar[i]), 1);
@@ -135,6 +150,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
+  const uint32_t rank = p.cluster ? cluster_ctarank() : 0u;
+  if (p.cluster) cluster_sync_all();  // the peer's barriers exist before anything is multicast at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -143,8 +160,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
-        const TileCoord tc = decode_tile(p, t, BLOCK_N);
+      TileCoord tc;
+      for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tc); ++i) {
         for (int kb = 0; kb < num_kb; ++kb) {
           const int tap = kb / p.chunks;
           const int ch = kb - tap * p.chunks;
@@ -156,11 +173,18 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int c = p.a_c0[s] + ch * BK;
           const int cx = tc.x0 + p.a_dx[s], cy = tc.y0 + p.a_dy[r], cp = p.a_p[r];
           tma_load_5d(smem_u32(st), &tmA, fb, c, cx, cp, cy, tc.sample);
-          tma_load_2d(smem_u32(st + L::kPlanes * L::kABytes), &tmB, fb, ch * BK, tap * p.n_total + tc.n0);
-          if (NSPLIT == 3) {
-            tma_load_5d(smem_u32(st + L::kABytes), &tmA, fb, c + p.a_lo_off, cx, cp, cy, tc.sample);
-            tma_load_2d(smem_u32(st + 2 * L::kABytes + L::kBBytes), &tmB, fb, ch * BK,
-                        (p.taps + tap) * p.n_total + tc.n0);
+          if (NSPLIT == 3) tma_load_5d(smem_u32(st + L::kABytes), &tmA, fb, c + p.a_lo_off, cx, cp, cy, tc.sample);
+          // weight tile: two boxes of BLOCK_N/2 rows per plane; in a cluster each CTA fetches one and multicasts it
+          constexpr int kHalfBytes = L::kBBytes / 2;
+          for (int pl = 0; pl < L::kPlanes; ++pl) {
+            uint8_t* bdst = st + L::kPlanes * L::kABytes + pl * L::kBBytes;
+            const int row = (pl * p.taps + tap) * p.n_total + tc.n0;
+            if (p.cluster) {
+              tma_load_2d_mc(smem_u32(bdst + rank * kHalfBytes), &tmB, fb, ch * BK, row + (int)rank * (BLOCK_N / 2), 3);
+            } else {
+              tma_load_2d(smem_u32(bdst), &tmB, fb, ch * BK, row);
+              tma_load_2d(smem_u32(bdst + kHalfBytes), &tmB, fb, ch * BK, row + BLOCK_N / 2);
+            }
           }
           if (++stage == stages) { stage = 0; phase ^= 1; }
         }
@@ -176,7 +200,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int stage = 0;
     uint32_t phase = 0;
     uint32_t acc = 0, acc_phase = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x) {
+    TileCoord tcm;
+    for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tcm); ++i) {
       mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);  // epilogue has drained this accumulator
       tc_fence_after();
       const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
@@ -198,7 +223,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               umma_bf16(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
             }
           }
-          umma_commit(smem_u32(&empty_bar[stage]));  // frees the smem slot when the MMAs retire
+          // frees the smem slot when the MMAs retire (in a cluster: in both CTAs, the peer multicasts into it)
+          if (p.cluster) umma_commit_mc(smem_u32(&empty_bar[stage]), 3);
+          else umma_commit(smem_u32(&empty_bar[stage]));
           if (kb == num_kb - 1) umma_commit(smem_u32(&tfull_bar[acc]));  // accumulator complete
         }
         __syncwarp();
@@ -216,11 +243,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int q = warp & 3;                   // TMEM lane quarter this warp may read
     int obuf = 0, ebuf = 0;
     uint8_t* gstaging = staging + (size_t)group * nbuf * L::kOutBufBytes;
-    int it = 0;
-    for (int t = blockIdx.x; t < p.total_tiles; t += gridDim.x, ++it) {
+    TileCoord tc;
+    for (int it = 0; get_tile(p, it, BLOCK_N, rank, &tc); ++it) {
       if (group >= ngroups || (ngroups == 2 && (it & 1) != group)) continue;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
-      const TileCoord tc = decode_tile(p, t, BLOCK_N);
       float* esa = es + (group * 2 + ebuf) * BLOCK_N;
       float* eha = eh + (group * 2 + ebuf) * BLOCK_N;
       ebuf ^= 1;
@@ -307,6 +333,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
+  if (p.cluster) cluster_sync_all();  // the peer may still multicast into / arrive on this CTA's shared memory
   if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
 }
 
