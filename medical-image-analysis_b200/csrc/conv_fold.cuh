@@ -47,7 +47,7 @@ struct ConvFoldParams {
   int H, W;
   int w_cout_total;  // output channels of the whole layer (row stride between filter taps in the packed weights)
   int w_co0;         // first output channel of the 32 this launch computes
-  int dbg;  // timing experiments only (B200AL_FOLD_DBG): 1 = no MMAs, 2 = no epilogue math/stores, 4 = no TMA stores, 8 = no TMA loads
+  int dbg;  // timing experiments only (B200AL_FOLD_DBG): 1 = no MMAs, 2 = no epilogue math/stores, 4 = no TMA stores, 8 = no TMA loads, 16 = print the MMA warp's loop cycles
 };
 
 constexpr int kFoldThreads = 320;   // TMA warp, MMA warp, 2 epilogue groups of 4 warps
@@ -195,96 +195,169 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
   } else if (warp == 1) {
     // ===================== UMMA issuer =====================
-    // The whole warp walks the loop (uniform control flow keeps the descriptor arithmetic on the
-    // uniform datapath); one elected lane issues the MMAs and commits.
+    // The tensor pipe runs dry whenever the issuing warp spends more than about one MMA's time away
+    // from issuing (tools/mma_bench.cu), so the bookkeeping is spread between the MMAs: the whole warp
+    // walks the loop (descriptor arithmetic stays on the uniform datapath), an elected lane issues,
+    // and the NEXT tile's barriers are polled and its descriptors built half-way through this tile.
     constexpr uint32_t idesc = umma_idesc_bf16(128, kFoldN);
     constexpr uint32_t kDescHi = umma_smem_desc_hi(kRowBytes);
+    constexpr int KS = L::kPacked ? 2 : CIN / 16;   // k16 steps per filter row and plane
+    constexpr int NA = 3 * KS;                      // A descriptors per plane
     mbar_wait(smem_u32(w_bar), 0);
     tc_fence_after();
-    const uint32_t w_hi = umma_smem_desc_lo(smem_u32(wsm));
-    const uint32_t w_lo = w_hi + ((3 * L::kWBlockBytes) >> 4);
+    const uint32_t w_base = umma_smem_desc_lo(smem_u32(wsm));
     const uint32_t ring_lo = umma_smem_desc_lo(smem_u32(ring));
+    // weight descriptors never change
+    uint64_t dwh[NA], dwl[NA];
+#pragma unroll
+    for (int r = 0; r < 3; ++r)
+#pragma unroll
+      for (int k = 0; k < KS; ++k) {
+        const uint32_t wo = w_base + ((r * L::kWBlockBytes + k * 32) >> 4);
+        dwh[r * KS + k] = make_desc(wo, kDescHi);
+        dwl[r * KS + k] = make_desc(wo + (L::kPacked ? 4u : (uint32_t)((3 * L::kWBlockBytes) >> 4)), kDescHi);
+      }
+    const int n_my = (int)((long long)p.total_tiles * (blockIdx.x + 1) / gridDim.x) -
+                     (int)((long long)p.total_tiles * blockIdx.x / gridDim.x);
+    const bool mma_on = !(p.dbg & 1);
+    const long long t_start = clock64();
     int slot = 0;
     uint32_t phase = 0;
     uint32_t acc = 0, acc_phase = 0;
-    const int n_my = (int)((long long)p.total_tiles * (blockIdx.x + 1) / gridDim.x) -
-                     (int)((long long)p.total_tiles * blockIdx.x / gridDim.x);
-    for (int i = 0; i < n_my; ++i) {
-      mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);
-      mbar_wait(smem_u32(&full_bar[slot]), phase);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * kFoldAccStride;
-      if (L::kPacked) {
-        const uint32_t a = ring_lo + (uint32_t)slot * (L::kSlotBytes >> 4);
+    bool ready = false;
+    auto a_descs = [&](uint64_t (&d)[NA], int sl, uint32_t extra) {
+#pragma unroll
+      for (int r = 0; r < 3; ++r)
+#pragma unroll
+        for (int k = 0; k < KS; ++k)
+          d[r * KS + k] = make_desc(ring_lo + (uint32_t)sl * (L::kSlotBytes >> 4) + extra +
+                                        ((r * 32 * kRowBytes + k * 32) >> 4), kDescHi);
+    };
+    if (L::kPacked) {
+      uint64_t dah[NA], dal[NA];
+      a_descs(dah, 0, 0);
+      a_descs(dal, 0, 4);  // lo plane: +64 bytes inside the row
+      for (int i = 0; i < n_my; ++i) {
+        if (!ready) {
+          mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);
+          mbar_wait(smem_u32(&full_bar[slot]), phase);
+        }
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kFoldAccStride;
+        if (mma_on && elect_one()) {
+#pragma unroll
+          for (int m = 0; m < NA / 2; ++m) {
+            umma_bf16(d_tmem, dah[m], dwh[m], idesc, m > 0 ? 1u : 0u);
+            if (NSPLIT == 3) {
+              umma_bf16(d_tmem, dah[m], dwl[m], idesc, 1u);
+              umma_bf16(d_tmem, dal[m], dwh[m], idesc, 1u);
+            }
+          }
+        }
+        int nslot = slot + 1;
+        uint32_t nphase = phase;
+        if (nslot == slots) { nslot = 0; nphase ^= 1; }
+        const uint32_t nacc = acc ^ 1, nacc_phase = acc_phase ^ (nacc == 0 ? 1u : 0u);
+        ready = false;
+        if (i + 1 < n_my)
+          ready = mbar_try_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
+                  mbar_try_wait(smem_u32(&full_bar[nslot]), nphase);
+        uint64_t nah[NA], nal[NA];
+        a_descs(nah, nslot, 0);
+        a_descs(nal, nslot, 4);
         if (elect_one()) {
+          if (mma_on) {
 #pragma unroll
-          for (int r = 0; r < 3; ++r) {
-            if (p.dbg & 1) break;
-#pragma unroll
-            for (int k = 0; k < 2; ++k) {
-              const uint32_t ah = a + ((r * 32 * kRowBytes + k * 32) >> 4), al = ah + 4;   // lo plane: +64 bytes
-              const uint32_t wh = w_hi + ((r * L::kWBlockBytes + k * 32) >> 4), wl = wh + 4;
-              umma_bf16(d_tmem, make_desc(ah, kDescHi), make_desc(wh, kDescHi), idesc, (r > 0 || k > 0) ? 1u : 0u);
+            for (int m = NA / 2; m < NA; ++m) {
+              umma_bf16(d_tmem, dah[m], dwh[m], idesc, 1u);
               if (NSPLIT == 3) {
-                umma_bf16(d_tmem, make_desc(ah, kDescHi), make_desc(wl, kDescHi), idesc, 1u);
-                umma_bf16(d_tmem, make_desc(al, kDescHi), make_desc(wh, kDescHi), idesc, 1u);
+                umma_bf16(d_tmem, dah[m], dwl[m], idesc, 1u);
+                umma_bf16(d_tmem, dal[m], dwh[m], idesc, 1u);
               }
             }
           }
           umma_commit(smem_u32(&empty_bar[slot]));
           umma_commit(smem_u32(&tfull_bar[acc]));
         }
-        __syncwarp();
-        if (++slot == slots) { slot = 0; phase ^= 1; }
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1;
-        continue;
+#pragma unroll
+        for (int m = 0; m < NA; ++m) { dah[m] = nah[m]; dal[m] = nal[m]; }
+        slot = nslot; phase = nphase; acc = nacc; acc_phase = nacc_phase;
       }
-      // hi plane of the activations: a_hi * w_hi (+ a_hi * w_lo)
-      {
-        const uint32_t a = ring_lo + (uint32_t)slot * (L::kSlotBytes >> 4);
+    } else {
+      // planes in separate slots: hi slot first (a_hi*w_hi, a_hi*w_lo), then lo slot (a_lo*w_hi)
+      uint64_t dah[NA];
+      a_descs(dah, 0, 0);
+      for (int i = 0; i < n_my; ++i) {
+        if (!ready) {
+          mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);
+          mbar_wait(smem_u32(&full_bar[slot]), phase);
+        }
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * kFoldAccStride;
+        if (mma_on && elect_one()) {
+#pragma unroll
+          for (int m = 0; m < NA / 2; ++m) {
+            umma_bf16(d_tmem, dah[m], dwh[m], idesc, m > 0 ? 1u : 0u);
+            if (NSPLIT == 3) umma_bf16(d_tmem, dah[m], dwl[m], idesc, 1u);
+          }
+        }
+        // second slot of this tile (lo plane) or, in bf16 mode, the next tile's slot
+        int slot1 = slot + 1;
+        uint32_t phase1 = phase;
+        if (slot1 == slots) { slot1 = 0; phase1 ^= 1; }
+        const uint32_t nacc = acc ^ 1, nacc_phase = acc_phase ^ (nacc == 0 ? 1u : 0u);
+        bool ready1 = false;
+        if (NSPLIT == 3) ready1 = mbar_try_wait(smem_u32(&full_bar[slot1]), phase1);
+        else if (i + 1 < n_my)
+          ready1 = mbar_try_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
+                   mbar_try_wait(smem_u32(&full_bar[slot1]), phase1);
+        uint64_t d1[NA];
+        a_descs(d1, slot1, 0);
         if (elect_one()) {
+          if (mma_on) {
 #pragma unroll
-          for (int r = 0; r < 3; ++r) {
-            if (p.dbg & 1) break;
-#pragma unroll
-            for (int k = 0; k < CIN / 16; ++k) {
-              const uint32_t ao = a + ((r * 32 * kRowBytes + k * 32) >> 4);
-              const uint32_t wo = (r * L::kWBlockBytes + k * 32) >> 4;
-              umma_bf16(d_tmem, make_desc(ao, kDescHi), make_desc(w_hi + wo, kDescHi), idesc,
-                        (r > 0 || k > 0) ? 1u : 0u);
-              if (NSPLIT == 3) umma_bf16(d_tmem, make_desc(ao, kDescHi), make_desc(w_lo + wo, kDescHi), idesc, 1u);
+            for (int m = NA / 2; m < NA; ++m) {
+              umma_bf16(d_tmem, dah[m], dwh[m], idesc, 1u);
+              if (NSPLIT == 3) umma_bf16(d_tmem, dah[m], dwl[m], idesc, 1u);
             }
           }
           umma_commit(smem_u32(&empty_bar[slot]));
           if (NSPLIT == 1) umma_commit(smem_u32(&tfull_bar[acc]));
         }
-        __syncwarp();
-      }
-      if (++slot == slots) { slot = 0; phase ^= 1; }
-      if (NSPLIT == 3) {
-        // lo plane: a_lo * w_hi
-        mbar_wait(smem_u32(&full_bar[slot]), phase);
+        if (NSPLIT == 1) {
+#pragma unroll
+          for (int m = 0; m < NA; ++m) dah[m] = d1[m];
+          ready = ready1;
+          slot = slot1; phase = phase1; acc = nacc; acc_phase = nacc_phase;
+          continue;
+        }
+        if (!ready1) mbar_wait(smem_u32(&full_bar[slot1]), phase1);
         tc_fence_after();
-        const uint32_t a = ring_lo + (uint32_t)slot * (L::kSlotBytes >> 4);
+        if (mma_on && elect_one()) {
+#pragma unroll
+          for (int m = 0; m < NA / 2; ++m) umma_bf16(d_tmem, d1[m], dwh[m], idesc, 1u);
+        }
+        int nslot = slot1 + 1;
+        uint32_t nphase = phase1;
+        if (nslot == slots) { nslot = 0; nphase ^= 1; }
+        ready = false;
+        if (i + 1 < n_my)
+          ready = mbar_try_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
+                  mbar_try_wait(smem_u32(&full_bar[nslot]), nphase);
+        a_descs(dah, nslot, 0);
         if (elect_one()) {
+          if (mma_on) {
 #pragma unroll
-          for (int r = 0; r < 3; ++r) {
-            if (p.dbg & 1) break;
-#pragma unroll
-            for (int k = 0; k < CIN / 16; ++k)
-              umma_bf16(d_tmem, make_desc(a + ((r * 32 * kRowBytes + k * 32) >> 4), kDescHi),
-                        make_desc(w_hi + ((r * L::kWBlockBytes + k * 32) >> 4), kDescHi), idesc, 1u);
+            for (int m = NA / 2; m < NA; ++m) umma_bf16(d_tmem, d1[m], dwh[m], idesc, 1u);
           }
-          umma_commit(smem_u32(&empty_bar[slot]));
+          umma_commit(smem_u32(&empty_bar[slot1]));
           umma_commit(smem_u32(&tfull_bar[acc]));
         }
-        __syncwarp();
-        if (++slot == slots) { slot = 0; phase ^= 1; }
+        slot = nslot; phase = nphase; acc = nacc; acc_phase = nacc_phase;
       }
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
     }
+    if ((p.dbg & 16) && blockIdx.x == 0 && lane == 0)
+      printf("b200al fold dbg: %d tiles, %lld cycles in the issue loop\n", n_my, clock64() - t_start);
   } else {
     // ===================== epilogue: two groups of 4 warps, alternating tiles =====================
     const int group = (warp - 2) >> 2;
