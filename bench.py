@@ -269,6 +269,26 @@ def run_b200(args):
     ms_e2e, picked_e2e = timed(step_e2e, max(1, min(args.steps, 2)))
     e2e_steps = max(1, min(args.steps, 2))
 
+    # kernel 3 of the north star on its own: softmax + entropy + mean over fp32 logits resident in HBM
+    # (805 MB per launch, larger than L2); algorithmic bytes = T*K*H*W*4 + 4 per image
+    unc = None
+    if rank == 0:
+        n_u = 128
+        lg = torch.randn((n_u, T_REPEATS, K_CLASSES, 256, 256), device=dev)
+        for _ in range(3):
+            eng.uncertainty_from_logits(lg, "entropy")
+        torch.cuda.synchronize()
+        u0, u1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        u0.record()
+        for _ in range(5):
+            eng.uncertainty_from_logits(lg, "entropy")
+        u1.record()
+        torch.cuda.synchronize()
+        unc_ms = u0.elapsed_time(u1) / 5
+        unc_bytes = n_u * (T_REPEATS * K_CLASSES * 256 * 256 * 4 + 4)
+        unc = (unc_bytes / (unc_ms / 1e3) / 1e9, unc_ms, unc_bytes)
+        del lg
+
     same = sorted(picked.cpu().tolist()) == sorted(picked_e2e.tolist())
     if rank == 0:
         tf_peak, hbm_peak, peak_src = peaks()
@@ -288,11 +308,20 @@ def run_b200(args):
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
                          "frac": achieved / tf_peak, "traffic": None,
-                         "kernel": "conv_tc_kernel (tcgen05 implicit GEMM, all 21 layers)",
+                         "kernel": "conv_fold_kernel + conv_tc_kernel (tcgen05 implicit GEMM, the 21 conv/convT layers)",
                          "launches_timed": int(conv_n), "avg_launch_ms": conv_ms / max(conv_n, 1),
-                         "flops_note": "algorithmic 2*MAC of the fp32 reference conv; bf16x3 issues 3 MMAs per product",
+                         "flops_note": "algorithmic 2*MAC of the fp32 reference conv; bf16x3 issues 3 MMAs per product, "
+                                       "so the tensor pipe runs at >= 3x this rate (frac_of_issue_ceiling = achieved / (peak/3))",
+                         "frac_of_issue_ceiling": (achieved * (3 if args.precision == "bf16x3" else 1)) / tf_peak,
                          "peak_source": peak_src},
         }
+        if unc:
+            line["roofline_hbm_kernel"] = {"bound": "hbm", "achieved": unc[0], "peak": hbm_peak, "unit": "GB/s",
+                                           "frac": unc[0] / hbm_peak, "traffic": None,
+                                           "kernel": "uncertainty_logits_kernel (softmax + entropy + per-image mean, "
+                                                     "128 images x T=8 x K=3 fp32 logits)",
+                                           "avg_launch_ms": unc[1], "bytes_per_launch": unc[2],
+                                           "peak_source": peak_src}
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(args.cpu_sample)
         print(json.dumps(line))
