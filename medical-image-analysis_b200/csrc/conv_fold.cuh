@@ -260,8 +260,8 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const uint32_t nacc = acc ^ 1, nacc_phase = acc_phase ^ (nacc == 0 ? 1u : 0u);
         ready = false;
         if (i + 1 < n_my)
-          ready = mbar_try_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
-                  mbar_try_wait(smem_u32(&full_bar[nslot]), nphase);
+          ready = mbar_test_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
+                  mbar_test_wait(smem_u32(&full_bar[nslot]), nphase);
         uint64_t nah[NA], nal[NA];
         a_descs(nah, nslot, 0);
         a_descs(nal, nslot, 4);
@@ -307,10 +307,10 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (slot1 == slots) { slot1 = 0; phase1 ^= 1; }
         const uint32_t nacc = acc ^ 1, nacc_phase = acc_phase ^ (nacc == 0 ? 1u : 0u);
         bool ready1 = false;
-        if (NSPLIT == 3) ready1 = mbar_try_wait(smem_u32(&full_bar[slot1]), phase1);
+        if (NSPLIT == 3) ready1 = mbar_test_wait(smem_u32(&full_bar[slot1]), phase1);
         else if (i + 1 < n_my)
-          ready1 = mbar_try_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
-                   mbar_try_wait(smem_u32(&full_bar[slot1]), phase1);
+          ready1 = mbar_test_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
+                   mbar_test_wait(smem_u32(&full_bar[slot1]), phase1);
         uint64_t d1[NA];
         a_descs(d1, slot1, 0);
         if (elect_one()) {
@@ -342,8 +342,8 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (nslot == slots) { nslot = 0; nphase ^= 1; }
         ready = false;
         if (i + 1 < n_my)
-          ready = mbar_try_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
-                  mbar_try_wait(smem_u32(&full_bar[nslot]), nphase);
+          ready = mbar_test_wait(smem_u32(&tempty_bar[nacc]), nacc_phase ^ 1) &&
+                  mbar_test_wait(smem_u32(&full_bar[nslot]), nphase);
         a_descs(dah, nslot, 0);
         if (elect_one()) {
           if (mma_on) {

@@ -6,6 +6,6 @@ for rep in $(seq $R); do
   for v in A B; do
     cp $D/lib$v.so $D/libb200al.so
     echo "== $v rep $rep"
-    python tools/gpu_diag.py perf bf16x3 64 $N 1 2>&1 | grep -E "scores|conv kernels|layer  0|layer  2|layer 10|layer 13|layer 16|layer 19|layer 20"
+    python tools/gpu_diag.py perf bf16x3 64 $N 1 2>&1 | grep -E "scores|conv kernels|layer  1|layer  3|layer  4|layer  8|layer 10|layer 13|layer 16|layer 18"
   done
 done
