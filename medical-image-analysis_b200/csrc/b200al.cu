@@ -59,6 +59,7 @@ struct Layer {
   float *scale = nullptr, *bias = nullptr, *shift = nullptr;
   CUtensorMap tmA, tmB, tmO;
   ConvTcParams p;
+  bool pair = false;   // CTA pairs running M=256 cta_group::2 MMAs (conv_tc.cuh, template PAIR)
   bool fold = false;   // column-folded kernel (conv_fold.cuh): stride-1 3x3, Cout = 32, Cin in {32, 64}
   ConvFoldParams fp;
   int slots = 0;
@@ -226,7 +227,7 @@ typedef void (*ConvKernelFn)(const CUtensorMap, const CUtensorMap, const CUtenso
 
 template <int BN, int BK, int CW>
 ConvKernelFn pick_split(int nsplit) {
-  return nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<BN, BK, 3, CW> : (ConvKernelFn)conv_tc_kernel<BN, BK, 1, CW>;
+  return nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<BN, BK, 3, CW, false> : (ConvKernelFn)conv_tc_kernel<BN, BK, 1, CW, false>;
 }
 template <int BN, int BK>
 ConvKernelFn pick_cw(int nsplit, int cw) {
@@ -235,7 +236,13 @@ ConvKernelFn pick_cw(int nsplit, int cw) {
   }
   return cw == 32 ? pick_split<BN, BK, 32>(nsplit) : nullptr;
 }
-ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw) {
+ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw, bool pair = false) {
+  if (pair) {  // BK = 64, CW = 32 only
+    if (bk != 64 || cw != 32) return nullptr;
+    if (bn == 128) return nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<128, 64, 3, 32, true> : (ConvKernelFn)conv_tc_kernel<128, 64, 1, 32, true>;
+    if (bn == 256) return nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<256, 64, 3, 32, true> : (ConvKernelFn)conv_tc_kernel<256, 64, 1, 32, true>;
+    return nullptr;
+  }
   if (bk == 32) {
     if (bn == 32) return pick_cw<32, 32>(nsplit, cw);
     if (bn == 64) return pick_cw<64, 32>(nsplit, cw);
@@ -249,10 +256,13 @@ ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw) {
   }
   return nullptr;
 }
-int stage_bytes(int bn, int bk, int nsplit) { return (nsplit == 3 ? 2 : 1) * (128 * bk * 2 + bn * bk * 2); }
+// pair: each CTA of the pair holds half of the weight tile's rows
+int stage_bytes(int bn, int bk, int nsplit, bool pair = false) {
+  return (nsplit == 3 ? 2 : 1) * (128 * bk * 2 + (pair ? bn / 2 : bn) * bk * 2);
+}
 int out_buf_bytes(int cw, int nsplit) { return (nsplit == 3 ? 2 : 1) * 128 * cw * 2; }
-int conv_smem_bytes(int bn, int bk, int nsplit, int stages, int cw, int nbufs_total) {
-  return stages * stage_bytes(bn, bk, nsplit) + nbufs_total * out_buf_bytes(cw, nsplit) + 1024 + 8 * bn * 4;
+int conv_smem_bytes(int bn, int bk, int nsplit, int stages, int cw, int nbufs_total, bool pair = false) {
+  return stages * stage_bytes(bn, bk, nsplit, pair) + nbufs_total * out_buf_bytes(cw, nsplit) + 1024 + 8 * bn * 4;
 }
 
 typedef void (*FoldKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const ConvFoldParams, const int);
@@ -301,19 +311,31 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   L.bn = n_total < bn_max ? n_total : bn_max;
   if (L.kind == KIND_CONVT && L.bn > L.cout && (L.bn % L.cout) != 0) L.bn = L.cout;
   if (L.bk == 32 && L.bn > 64) L.bn = 64;
+  // The generic kernel is bound by the L2->SM operand stream (64 KB per 12 MMAs at 128x128 tiles is twice
+  // what the L2 delivers per SM).  CTA pairs (cta_group::2, M = 256) split every weight tile between two
+  // SMs, and N = 256 tiles halve the activation bytes per flop again.
+  // Measured (profiles/r01_perlayer_v7_pair.txt): 256-wide pair tiles gain 3-15% on the Cout >= 256 layers,
+  // 128-wide pair tiles LOSE 30-50% against the single-CTA 128x128 tile, so pairs are used at N >= 256 only.
+  L.pair = L.bk == 64 && n_total >= env_int("B200AL_PAIR_MIN_N", 256) && env_int("B200AL_PAIR", 1) != 0;
+  if (L.pair) {
+    const int pbn = env_int("B200AL_PAIR_BN", 256);
+    L.bn = n_total < pbn ? n_total : pbn;
+    if (L.bn != 128 && L.bn != 256) L.pair = false, L.bn = n_total < bn_max ? n_total : bn_max;
+  }
   // smem policy: small tiles aim for 2 CTAs/SM (<= ~110 KB each), large ones take the whole SM.
-  const int sb = stage_bytes(L.bn, L.bk, ctx->nsplit);
+  const int sb = stage_bytes(L.bn, L.bk, ctx->nsplit, L.pair);
   const int kMaxSmem = 227 * 1024;
   const int fixed = 1024 + 8 * L.bn * 4;
   L.cw = (L.bn >= 64 && L.cout >= 64) ? 64 : 32;
   L.cw = env_int("B200AL_CW", L.cw) == 32 ? 32 : L.cw;
+  if (L.pair) L.cw = 32;
   // Short k-loops (full-resolution layers, transposed convs) are epilogue-heavy: two epilogue groups.
   // Long k-loops are MMA-bound: one group, the shared memory goes to pipeline stages instead.
   const int num_kb = (L.kind == KIND_CONV3 ? 9 : 1) * (L.cin / L.bk);
   L.ngroups = env_int("B200AL_NGROUPS", num_kb <= 18 ? 2 : 1);
   L.nbuf = L.ngroups == 2 ? 1 : 2;
   const int budget2 = env_int("B200AL_SMEM_BUDGET", 110 * 1024);
-  int st = (budget2 - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
+  int st = L.pair ? 0 : (budget2 - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
   if (st < 3) {  // one CTA per SM
     st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
     if (st < 3 && L.ngroups * L.nbuf > 1) {
@@ -439,7 +461,7 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
     CUDA_TRY(ctx, cudaGetLastError());
     return 0;
   }
-  ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw);
+  ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw, L.pair);
   if (!fn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no conv kernel for BN=%d BK=%d", L.bn, L.bk);
   ConvTcParams q = p;
   q.n_tiles = p.n_total / L.bn;
@@ -447,10 +469,11 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
   const int resident = ctx->sm_count * L.ctas_per_sm;
   // CTA pairs with multicast weight tiles: pixel tiles come in pairs, one CTA per SM
   const int m_tiles = S * p.tiles_x * p.tiles_y;
-  q.cluster = (L.ctas_per_sm == 1 && m_tiles % 2 == 0 && q.total_tiles >= 4 && env_int("B200AL_CLUSTER", 1)) ? 1 : 0;
+  if (L.pair && m_tiles % 2) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "odd number of pixel tiles in a paired layer");
+  q.cluster = L.pair ? 1 : 0;
   unsigned nblk = (unsigned)(q.total_tiles < resident ? q.total_tiles : resident);
   if (q.cluster) nblk &= ~1u;
-  const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups);
+  const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups, L.pair);
   const bool t = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
   if (t) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
   {
@@ -601,18 +624,19 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
     // rows: conv [2 planes][9 taps][Cout]; convT [2 planes][1][4*Cout]
     // (boxes of BN/2 rows: a weight tile is fetched as two halves, see conv_tc.cuh)
     TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn / 2));
-    ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw);
+    ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw, L.pair);
     if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d CW=%d", L.bn, L.bk, L.cw); b200al_ctx_destroy(ctx); return rc; }
-    const int smem_l = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups);
+    const int smem_l = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups, L.pair);
     TRY_CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     int occ = 0;
     TRY_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kConvThreads, smem_l));
     const int tmem_limit = 512 / (2 * L.bn);  // two accumulator stages per CTA
     L.ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
     if (L.ctas_per_sm > 2) L.ctas_per_sm = 2;
+    if (L.pair) L.ctas_per_sm = 1;
     if (env_int("B200AL_VERBOSE", 0))
-      fprintf(stderr, "b200al plan: kind=%d %d->%d s%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d\n", L.kind,
-              L.cin, L.cout, L.stride, L.bn, L.bk, L.stages, L.cw, L.nbuf, L.ngroups, smem_l, L.ctas_per_sm);
+      fprintf(stderr, "b200al plan: kind=%d %d->%d s%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d pair=%d\n", L.kind,
+              L.cin, L.cout, L.stride, L.bn, L.bk, L.stages, L.cw, L.nbuf, L.ngroups, smem_l, L.ctas_per_sm, (int)L.pair);
   }
   TRY_RC(dev_alloc(ctx, &ctx->first_w, 32 * 9));
   TRY_RC(dev_alloc(ctx, &ctx->first_bias, 32));

@@ -51,19 +51,19 @@ struct ConvTcParams {
   int shuffle;  // 1: transposed conv, column n -> (quad=n/cout, co=n%cout), pixel (2y+quad/2, 2x+quad%2)
   int cout;     // channels per quad (== n_total when !shuffle)
   int write_lo;
-  // 1: launched as clusters of 2 CTAs that work on two adjacent pixel tiles of the same n-tile; each CTA
-  // fetches half of every weight tile and multicasts it to both (halves the L2->SM weight traffic)
+  // 1: launched as clusters of 2 CTAs (template PAIR) that run one M=256 cta_group::2 MMA over two adjacent
+  // pixel tiles of the same n-tile; each CTA loads its own pixel tile and HALF of the weight tile
   int cluster;
 };
 
 constexpr int kConvThreads = 320;  // TMA warp + MMA warp + 2 epilogue groups of 4 warps
 
 // smem: [stages x (A planes, B planes)] [nbuf x planes x 128 x CW staging for the TMA store] [barriers] [affine]
-template <int BLOCK_N, int BK, int NSPLIT, int CW>
+template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR = false>
 struct ConvTcSmem {
   static constexpr int kPlanes = (NSPLIT == 3) ? 2 : 1;
   static constexpr int kABytes = 128 * BK * 2;
-  static constexpr int kBBytes = BLOCK_N * BK * 2;
+  static constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * BK * 2;  // rows of B held by this CTA
   static constexpr int kStageBytes = kPlanes * (kABytes + kBBytes);
   static constexpr int kOutWarpBytes = 32 * CW * 2;                  // one warp's 32 rows of one plane
   static constexpr int kOutBufBytes = kPlanes * 4 * kOutWarpBytes;   // one staging buffer
@@ -99,11 +99,11 @@ __device__ __forceinline__ bool get_tile(const ConvTcParams& p, int i, int block
   return true;
 }
 
-template <int BLOCK_N, int BK, int NSPLIT, int CW>
+template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR>
 __global__ void __launch_bounds__(kConvThreads)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const ConvTcParams p, const int stages, const int nbuf, const int ngroups) {
-  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW>;
+  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW, PAIR>;
   static_assert(BLOCK_N % CW == 0 && (CW == 32 || CW == 64), "bad store chunk width");
   constexpr uint32_t kRowBytes = BK * 2;  // 128 -> SW128, 64 -> SW64
   constexpr uint32_t kTmemCols = 2 * BLOCK_N;  // two accumulator stages (power of two >= 64)
@@ -135,23 +135,23 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < stages; ++i) {
-      mbar_init(smem_u32(&full_bar[i]), 1);
-      mbar_init(smem_u32(&empty_bar[i]), p.cluster ? 2 : 1);  // cluster: released by both CTAs' MMA warps
+      mbar_init(smem_u32(&full_bar[i]), PAIR ? 2 : 1);  // pair: both CTAs' producers arrive on the leader's barrier
+      mbar_init(smem_u32(&empty_bar[i]), 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&tfull_bar[i]), 1);
-      mbar_init(smem_u32(&tempty_bar[i]), 4);  // one arrive per epilogue warp
+      mbar_init(smem_u32(&tempty_bar[i]), PAIR ? 8 : 4);  // one arrive per epilogue warp (of both CTAs)
     }
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(smem_u32(tmem_slot), kTmemCols);
-    tmem_relinquish();
+    if (PAIR) { tmem_alloc_pair(smem_u32(tmem_slot), kTmemCols); tmem_relinquish_pair(); }
+    else { tmem_alloc(smem_u32(tmem_slot), kTmemCols); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
-  const uint32_t rank = p.cluster ? cluster_ctarank() : 0u;
-  if (p.cluster) cluster_sync_all();  // the peer's barriers exist before anything is multicast at them
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
+  if (PAIR) cluster_sync_all();  // the peer's barriers and TMEM exist before anything is signalled at them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -167,23 +167,31 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int ch = kb - tap * p.chunks;
           const int r = tap / 3, s = tap - r * 3;
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
-          const uint32_t fb = smem_u32(&full_bar[stage]);
-          mbar_arrive_expect_tx(fb, L::kStageBytes);
           uint8_t* st = smem + (size_t)stage * L::kStageBytes;
           const int c = p.a_c0[s] + ch * BK;
           const int cx = tc.x0 + p.a_dx[s], cy = tc.y0 + p.a_dy[r], cp = p.a_p[r];
-          tma_load_5d(smem_u32(st), &tmA, fb, c, cx, cp, cy, tc.sample);
-          if (NSPLIT == 3) tma_load_5d(smem_u32(st + L::kABytes), &tmA, fb, c + p.a_lo_off, cx, cp, cy, tc.sample);
-          // weight tile: two boxes of BLOCK_N/2 rows per plane; in a cluster each CTA fetches one and multicasts it
-          constexpr int kHalfBytes = L::kBBytes / 2;
-          for (int pl = 0; pl < L::kPlanes; ++pl) {
-            uint8_t* bdst = st + L::kPlanes * L::kABytes + pl * L::kBBytes;
-            const int row = (pl * p.taps + tap) * p.n_total + tc.n0;
-            if (p.cluster) {
-              tma_load_2d_mc(smem_u32(bdst + rank * kHalfBytes), &tmB, fb, ch * BK, row + (int)rank * (BLOCK_N / 2), 3);
-            } else {
+          if (PAIR) {
+            // this CTA's pixel tile and its half of the weight tile; all bytes complete on the LEADER's barrier
+            const uint32_t own = smem_u32(&full_bar[stage]);
+            const uint32_t fb = rank == 0 ? own : mapa_shared(own, 0);
+            if (rank == 0) mbar_arrive_expect_tx(own, 2 * L::kStageBytes);
+            else mbar_arrive_remote(fb);
+            tma_load_5d_pair(smem_u32(st), &tmA, fb, c, cx, cp, cy, tc.sample);
+            if (NSPLIT == 3) tma_load_5d_pair(smem_u32(st + L::kABytes), &tmA, fb, c + p.a_lo_off, cx, cp, cy, tc.sample);
+            for (int pl = 0; pl < L::kPlanes; ++pl)
+              tma_load_2d_pair(smem_u32(st + L::kPlanes * L::kABytes + pl * L::kBBytes), &tmB, fb, ch * BK,
+                               (pl * p.taps + tap) * p.n_total + tc.n0 + (int)rank * (BLOCK_N / 2));
+          } else {
+            const uint32_t fb = smem_u32(&full_bar[stage]);
+            mbar_arrive_expect_tx(fb, L::kStageBytes);
+            tma_load_5d(smem_u32(st), &tmA, fb, c, cx, cp, cy, tc.sample);
+            if (NSPLIT == 3) tma_load_5d(smem_u32(st + L::kABytes), &tmA, fb, c + p.a_lo_off, cx, cp, cy, tc.sample);
+            // the weight tile is fetched as two boxes of BLOCK_N/2 rows per plane (one tensor map serves both modes)
+            for (int pl = 0; pl < L::kPlanes; ++pl) {
+              uint8_t* bdst = st + L::kPlanes * L::kABytes + pl * L::kBBytes;
+              const int row = (pl * p.taps + tap) * p.n_total + tc.n0;
               tma_load_2d(smem_u32(bdst), &tmB, fb, ch * BK, row);
-              tma_load_2d(smem_u32(bdst + kHalfBytes), &tmB, fb, ch * BK, row + BLOCK_N / 2);
+              tma_load_2d(smem_u32(bdst + L::kBBytes / 2), &tmB, fb, ch * BK, row + BLOCK_N / 2);
             }
           }
           if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -191,48 +199,63 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       }
     }
   } else if (warp == 1) {
-    // ===================== UMMA issuer =====================
+    // ===================== UMMA issuer (pair: the leader CTA only) =====================
     // The whole warp walks the loop (uniform control flow keeps the descriptor arithmetic on the
     // uniform datapath); one elected lane issues the MMAs and commits.
-    constexpr uint32_t idesc = umma_idesc_bf16(128, BLOCK_N);
-    constexpr uint32_t kDescHi = umma_smem_desc_hi(kRowBytes);
-    const uint32_t ring_lo = umma_smem_desc_lo(smem_u32(smem));
-    int stage = 0;
-    uint32_t phase = 0;
-    uint32_t acc = 0, acc_phase = 0;
-    TileCoord tcm;
-    for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tcm); ++i) {
-      mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);  // epilogue has drained this accumulator
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(smem_u32(&full_bar[stage]), phase);
+    if (!PAIR || rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(PAIR ? 256 : 128, BLOCK_N);
+      constexpr uint32_t kDescHi = umma_smem_desc_hi(kRowBytes);
+      const uint32_t ring_lo = umma_smem_desc_lo(smem_u32(smem));
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t acc = 0, acc_phase = 0;
+      TileCoord tcm;
+      for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tcm); ++i) {
+        mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);  // epilogue(s) have drained this accumulator
         tc_fence_after();
-        const uint32_t a_hi = ring_lo + (uint32_t)stage * (L::kStageBytes >> 4);
-        const uint32_t a_lo = a_hi + (L::kABytes >> 4);
-        const uint32_t b_hi = a_hi + ((L::kPlanes * L::kABytes) >> 4);
-        const uint32_t b_lo = b_hi + (L::kBBytes >> 4);
-        if (elect_one()) {
+        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(smem_u32(&full_bar[stage]), phase);
+          tc_fence_after();
+          const uint32_t a_hi = ring_lo + (uint32_t)stage * (L::kStageBytes >> 4);
+          const uint32_t a_lo = a_hi + (L::kABytes >> 4);
+          const uint32_t b_hi = a_hi + ((L::kPlanes * L::kABytes) >> 4);
+          const uint32_t b_lo = b_hi + (L::kBBytes >> 4);
+          if (elect_one()) {
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            const uint64_t da = make_desc(a_hi + 2 * k, kDescHi);
-            const uint64_t db = make_desc(b_hi + 2 * k, kDescHi);
-            umma_bf16(d_tmem, da, db, idesc, (kb > 0 || k > 0) ? 1u : 0u);
-            if (NSPLIT == 3) {
-              umma_bf16(d_tmem, da, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
-              umma_bf16(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
+            for (int k = 0; k < BK / 16; ++k) {
+              const uint64_t da = make_desc(a_hi + 2 * k, kDescHi);
+              const uint64_t db = make_desc(b_hi + 2 * k, kDescHi);
+              const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
+              if (PAIR) {
+                umma_bf16_pair(d_tmem, da, db, idesc, accum);
+                if (NSPLIT == 3) {
+                  umma_bf16_pair(d_tmem, da, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
+                  umma_bf16_pair(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
+                }
+              } else {
+                umma_bf16(d_tmem, da, db, idesc, accum);
+                if (NSPLIT == 3) {
+                  umma_bf16(d_tmem, da, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
+                  umma_bf16(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
+                }
+              }
+            }
+            // frees the smem slot (pair: in both CTAs) when the MMAs retire; last k-block: accumulator complete
+            if (PAIR) {
+              umma_commit_pair(smem_u32(&empty_bar[stage]));
+              if (kb == num_kb - 1) umma_commit_pair(smem_u32(&tfull_bar[acc]));
+            } else {
+              umma_commit(smem_u32(&empty_bar[stage]));
+              if (kb == num_kb - 1) umma_commit(smem_u32(&tfull_bar[acc]));
             }
           }
-          // frees the smem slot when the MMAs retire (in a cluster: in both CTAs, the peer multicasts into it)
-          if (p.cluster) umma_commit_mc(smem_u32(&empty_bar[stage]), 3);
-          else umma_commit(smem_u32(&empty_bar[stage]));
-          if (kb == num_kb - 1) umma_commit(smem_u32(&tfull_bar[acc]));  // accumulator complete
+          __syncwarp();
+          if (++stage == stages) { stage = 0; phase ^= 1; }
         }
-        __syncwarp();
-        if (++stage == stages) { stage = 0; phase ^= 1; }
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
       }
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
     }
   } else {
     // ===================== epilogue: two groups of 4 warps =====================
@@ -279,7 +302,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (c0 + CW >= BLOCK_N && h == CW / 32 - 1) {  // last read of this accumulator: hand it back
             tc_fence_before();
             __syncwarp();
-            if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
+            if (elect_one()) {
+              if (PAIR && rank != 0) mbar_arrive_remote(mapa_shared(smem_u32(&tempty_bar[acc]), 0));
+              else mbar_arrive(smem_u32(&tempty_bar[acc]));
+            }
           }
           uint32_t hi[16], lo[16];
 #pragma unroll
@@ -333,8 +359,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   tc_fence_before();
   __syncthreads();
-  if (p.cluster) cluster_sync_all();  // the peer may still multicast into / arrive on this CTA's shared memory
-  if (warp == 2) tmem_dealloc(tmem_base, kTmemCols);
+  if (PAIR) cluster_sync_all();  // the peer may still arrive on this CTA's barriers / the leader's MMAs write this TMEM
+  if (warp == 2) {
+    if (PAIR) tmem_dealloc_pair(tmem_base, kTmemCols);
+    else tmem_dealloc(tmem_base, kTmemCols);
+  }
 }
 
 }  // namespace b200al
