@@ -41,6 +41,7 @@ enum b200al_score_mode {    /* which selector's score */
   B200AL_CONFIDENCE = 2     /* ConfidenceSelector.cal_scores  confidence_selector.py:45-47 */
 };
 enum b200al_metric { B200AL_L2 = 0, B200AL_COSINE = 1 }; /* CoresetSelector(metric=...) */
+enum b200al_criteria { B200AL_MIN = 0, B200AL_MEAN = 1 }; /* CoresetSelector(coreset_criteria=...) */
 enum b200al_precision {
   B200AL_BF16X3 = 0, /* bf16 hi/lo split operands, 3 MMAs per k-step, fp32 accumulate (default; parity grade) */
   B200AL_BF16 = 1    /* single bf16 operands (fast; does not meet the 2e-2 logit tolerance) */
@@ -113,18 +114,21 @@ int b200al_uncertainty_from_logits(b200al_ctx* ctx, const float* d_logits, int n
 int b200al_topk(b200al_ctx* ctx, const float* d_scores, int n, int k, int64_t base_pos, float* d_out_scores,
                 int64_t* d_out_pos, void* stream);
 
-/* k-center greedy (coreset_selector.py:19-51, criteria "min").
- * init: d_mind[i] = min_j dist(emb_i, centre_j) over L centres (the labeled
- * rows, coreset_selector.py:85,226); accumulate != 0 folds into existing mind.
+/* k-center greedy (coreset_selector.py:19-51).  criteria B200AL_MIN (":34", d_state = float [n] running minimum
+ * distance to the centres) or B200AL_MEAN (":36", d_state = double [n] running SUM of distances; the mean's
+ * divisor is the same for every row).
+ * init: folds the L initial centres (the labeled rows, coreset_selector.py:85,226) into d_state;
+ * accumulate != 0 continues from the existing state.
  * For COSINE both matrices must hold rows normalised by b200al_normalize_rows. */
 int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, int D, const float* d_centres, int L, int metric,
-                        float* d_mind, int accumulate, void* stream);
-/* run: `budget` greedy steps over rows not marked in d_taken (uint8 [n]);
+                        int criteria, void* d_state, int accumulate, void* stream);
+/* run: `budget` greedy steps over rows not marked in d_taken (uint8 [n]); n_centres = number of centres already
+ * folded into d_state (the divisor of the mean).
  * d_picks [budget] int64 row indices in selection order (-1 when exhausted),
- * d_pick_vals nullable [budget] = the max-min distance of each pick.
- * d_mind / d_taken are updated in place. */
-int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, float* d_mind, uint8_t* d_taken,
-                       int budget, int64_t* d_picks, float* d_pick_vals, void* stream);
+ * d_pick_vals nullable [budget] = the criterion value of each pick (max-min distance / max mean distance).
+ * d_state / d_taken are updated in place. */
+int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, int criteria, int n_centres,
+                       void* d_state, uint8_t* d_taken, int budget, int64_t* d_picks, float* d_pick_vals, void* stream);
 int b200al_normalize_rows(b200al_ctx* ctx, const float* d_in, float* d_out, int n, int D, void* stream);
 
 /* Introspection for benches / tests. */

@@ -24,6 +24,8 @@ U8, F32 = 0, 1
 
 MODES = {"entropy": ENTROPY, "margin": MARGIN, "confidence": CONFIDENCE}
 METRICS = {"l2": L2, "cosine": COSINE}
+CRIT_MIN, CRIT_MEAN = 0, 1
+CRITERIA = {"min": CRIT_MIN, "mean": CRIT_MEAN}
 PRECISIONS = {"bf16x3": BF16X3, "bf16": BF16}
 
 
@@ -56,10 +58,10 @@ PROTOTYPES = {
     "b200al_uncertainty_from_logits": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                                  C.c_float, C.c_void_p, C.c_void_p]),
     "b200al_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
-    "b200al_kcenter_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int,
+    "b200al_kcenter_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                       C.c_void_p, C.c_int, C.c_void_p]),
-    "b200al_kcenter_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
-                                     C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200al_kcenter_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                     C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200al_normalize_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "b200al_kernel_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "b200al_conv_time_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64), C.POINTER(C.c_double)]),

@@ -250,32 +250,38 @@ class Engine:
         return vals, pos
 
     # --------------------------------------------------------------- k-center
-    def kcenter(self, feats: torch.Tensor, n_init: int, budget: int, metric: str = "l2", return_vals: bool = False):
+    def kcenter(self, feats: torch.Tensor, n_init: int, budget: int, metric: str = "l2", return_vals: bool = False,
+                criteria: str = "min"):
         """k-center greedy over rows of `feats` [n,D] (fp32, device); rows
-        [0,n_init) are the initial centres (labeled set).  Returns row indices
-        (int64, selection order)."""
+        [0,n_init) are the initial centres (labeled set).  criteria "min"
+        (farthest point from its nearest centre) or "mean" (largest mean
+        distance to all centres), coreset_selector.py:33-36.  Returns row
+        indices (int64, selection order)."""
         feats = feats.to(device=self.device, dtype=torch.float32).contiguous()
         n, D = feats.shape
         if n_init < 1:
             raise ValueError("k-center needs at least one labeled row (the reference falls back to random selection)")
+        if criteria not in _lib.CRITERIA:
+            raise RuntimeError(f"coreset_criteria {criteria} is undefined")  # coreset_selector.py:38-40
         budget = min(int(budget), n - n_init)
         picks = torch.empty(budget, dtype=torch.int64, device=self.device)
         vals = torch.empty(budget, dtype=torch.float32, device=self.device)
         if budget <= 0:
             return (picks, vals) if return_vals else picks
         st = self._stream()
-        m = _lib.METRICS[metric]
+        m, c = _lib.METRICS[metric], _lib.CRITERIA[criteria]
         with torch.cuda.device(self.device):
             if metric == "cosine":
                 normed = torch.empty_like(feats)
                 self._check(self.lib.b200al_normalize_rows(self.ctx, self._ptr(feats), self._ptr(normed), n, D, st))
                 feats = normed
-            mind = torch.empty(n, dtype=torch.float32, device=self.device)
+            # running minimum (fp32) or running sum (fp64) of the distances to the centres
+            state = torch.empty(n, dtype=torch.float64 if criteria == "mean" else torch.float32, device=self.device)
             taken = torch.zeros(n, dtype=torch.uint8, device=self.device)
             taken[:n_init] = 1
-            self._check(self.lib.b200al_kcenter_init(self.ctx, self._ptr(feats), n, D, self._ptr(feats), n_init, m,
-                                                     self._ptr(mind), 0, st))
-            self._check(self.lib.b200al_kcenter_run(self.ctx, self._ptr(feats), n, D, m, self._ptr(mind),
+            self._check(self.lib.b200al_kcenter_init(self.ctx, self._ptr(feats), n, D, self._ptr(feats), n_init, m, c,
+                                                     self._ptr(state), 0, st))
+            self._check(self.lib.b200al_kcenter_run(self.ctx, self._ptr(feats), n, D, m, c, n_init, self._ptr(state),
                                                     self._ptr(taken), budget, self._ptr(picks), self._ptr(vals), st))
         return (picks, vals) if return_vals else picks
 

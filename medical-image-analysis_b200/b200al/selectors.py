@@ -221,7 +221,7 @@ def _embed_positions(eng: Engine, src: PoolSource, positions: list[int]) -> torc
 
 class B200CoresetSelector(_B200Base):
     """CoresetSelector (src/activelearning/coreset_selector.py:54) for
-    metric in {l2, cosine}, coreset_criteria 'min', model features only."""
+    metric in {l2, cosine}, coreset_criteria in {min, mean}, model features only."""
 
     def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8,
                  metric: str = "cosine", coreset_criteria: str = "min", coreset_fusion: str = "add",
@@ -229,13 +229,12 @@ class B200CoresetSelector(_B200Base):
         super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
         if metric not in ("l2", "cosine"):
             raise NotImplementedError(f"metric {metric!r}: only 'l2' and 'cosine' are supported")
-        if coreset_criteria != "min":
-            if coreset_criteria == "mean":
-                raise NotImplementedError("coreset_criteria='mean' is not supported yet")
+        if coreset_criteria not in ("min", "mean"):
             raise RuntimeError(f"coreset_criteria {coreset_criteria} is undefined")  # coreset_selector.py:38-40
         if feature_path is not None or loaded_feature_weight != 0.0:
             raise NotImplementedError("externally loaded features (feature_path / loaded_feature_weight) are not supported")
         self.metric = metric
+        self.coreset_criteria = coreset_criteria
 
     def select_next_batch(self, active_dataset, select_num: int, model, device):
         labeled_size, pool_size = active_dataset.get_size()
@@ -251,7 +250,7 @@ class B200CoresetSelector(_B200Base):
         emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
         emb_p = D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi))))
         feats = torch.cat([emb_l, emb_p], 0)
-        picks = eng.kcenter(feats, labeled_size, select_num, self.metric)
+        picks = eng.kcenter(feats, labeled_size, select_num, self.metric, criteria=self.coreset_criteria)
         return [all_list[i] for i in picks.tolist()]
 
 

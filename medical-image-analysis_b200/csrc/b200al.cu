@@ -946,14 +946,20 @@ extern "C" int b200al_topk(b200al_ctx* ctx, const float* d_scores, int n, int k,
 // ---------------------------------------------------------------------------
 namespace {
 template <int NV>
-void launch_kc_init(const float* emb, int n, const float* centres, int L, int metric, float* mind, int accumulate,
-                    int blocks, cudaStream_t st) {
-  kcenter_init_kernel<NV, (NV <= 4 ? 4 : 2)><<<blocks, 256, 0, st>>>(emb, n, centres, L, metric, mind, accumulate);
+void launch_kc_init(const float* emb, int n, const float* centres, int L, int metric, int criteria, void* state,
+                    int accumulate, int blocks, cudaStream_t st) {
+  if (criteria == B200AL_MEAN)
+    kcenter_init_mean_kernel<NV, (NV <= 4 ? 4 : 2)><<<blocks, 256, 0, st>>>(emb, n, centres, L, metric, (double*)state, accumulate);
+  else
+    kcenter_init_kernel<NV, (NV <= 4 ? 4 : 2)><<<blocks, 256, 0, st>>>(emb, n, centres, L, metric, (float*)state, accumulate);
 }
 template <int NV>
-void launch_kc_step(const float* emb, int n, const float* centre, int do_update, int metric, float* mind,
-                    const uint8_t* taken, float* pv, int* pi, int blocks, cudaStream_t st) {
-  kcenter_step_kernel<NV><<<blocks, 256, 0, st>>>(emb, n, centre, do_update, metric, mind, taken, pv, pi);
+void launch_kc_step(const float* emb, int n, const float* centre, int do_update, int metric, int criteria, void* state,
+                    double inv_count, const uint8_t* taken, float* pv, int* pi, int blocks, cudaStream_t st) {
+  if (criteria == B200AL_MEAN)
+    kcenter_step_mean_kernel<NV><<<blocks, 256, 0, st>>>(emb, n, centre, do_update, metric, (double*)state, inv_count, taken, pv, pi);
+  else
+    kcenter_step_kernel<NV><<<blocks, 256, 0, st>>>(emb, n, centre, do_update, metric, (float*)state, taken, pv, pi);
 }
 int check_dim(b200al_ctx* ctx, int D) {
   if (D != 128 && D != 256 && D != 512 && D != 1024)
@@ -974,34 +980,38 @@ extern "C" int b200al_normalize_rows(b200al_ctx* ctx, const float* d_in, float* 
 }
 
 extern "C" int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, int D, const float* d_centres, int L,
-                                   int metric, float* d_mind, int accumulate, void* stream) {
+                                   int metric, int criteria, void* d_state, int accumulate, void* stream) {
   if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
   if (n == 0) return B200AL_OK;
-  if (!d_emb || !d_centres || !d_mind || n < 0) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (!d_emb || !d_centres || !d_state || n < 0) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
   if (L < 1) return set_err(ctx, B200AL_ERR_ARG, "k-center needs at least one initial centre (L >= 1)");
   if (metric != B200AL_L2 && metric != B200AL_COSINE) return set_err(ctx, B200AL_ERR_ARG, "bad metric");
+  if (criteria != B200AL_MIN && criteria != B200AL_MEAN) return set_err(ctx, B200AL_ERR_ARG, "bad criteria");
   if (int rc = check_dim(ctx, D)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   int blocks = (n + 31) / 32;  // 8 warps x 4 rows
   if (blocks > ctx->sm_count * 8) blocks = ctx->sm_count * 8;
   switch (D / 128) {
-    case 1: launch_kc_init<1>(d_emb, n, d_centres, L, metric, d_mind, accumulate, blocks, st); break;
-    case 2: launch_kc_init<2>(d_emb, n, d_centres, L, metric, d_mind, accumulate, blocks, st); break;
-    case 4: launch_kc_init<4>(d_emb, n, d_centres, L, metric, d_mind, accumulate, blocks, st); break;
-    case 8: launch_kc_init<8>(d_emb, n, d_centres, L, metric, d_mind, accumulate, blocks, st); break;
+    case 1: launch_kc_init<1>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
+    case 2: launch_kc_init<2>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
+    case 4: launch_kc_init<4>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
+    case 8: launch_kc_init<8>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
   }
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return B200AL_OK;
 }
 
-extern "C" int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, float* d_mind,
-                                  uint8_t* d_taken, int budget, int64_t* d_picks, float* d_pick_vals, void* stream) {
+extern "C" int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, int criteria,
+                                  int n_centres, void* d_state, uint8_t* d_taken, int budget, int64_t* d_picks,
+                                  float* d_pick_vals, void* stream) {
   if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
   if (budget == 0) return B200AL_OK;
-  if (!d_emb || !d_mind || !d_taken || !d_picks || n < 1 || budget < 0) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (!d_emb || !d_state || !d_taken || !d_picks || n < 1 || budget < 0) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
   if (metric != B200AL_L2 && metric != B200AL_COSINE) return set_err(ctx, B200AL_ERR_ARG, "bad metric");
+  if (criteria != B200AL_MIN && criteria != B200AL_MEAN) return set_err(ctx, B200AL_ERR_ARG, "bad criteria");
+  if (criteria == B200AL_MEAN && n_centres < 1) return set_err(ctx, B200AL_ERR_ARG, "mean criteria needs n_centres >= 1");
   if (int rc = check_dim(ctx, D)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
@@ -1010,11 +1020,12 @@ extern "C" int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, in
   if (blocks < 1) blocks = 1;
   for (int step = 0; step < budget; ++step) {
     const int upd = step > 0;
+    const double inv = 1.0 / (double)(n_centres + step);  // centres folded in once this step's update is done
     switch (D / 128) {
-      case 1: launch_kc_step<1>(d_emb, n, ctx->kc_centre, upd, metric, d_mind, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
-      case 2: launch_kc_step<2>(d_emb, n, ctx->kc_centre, upd, metric, d_mind, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
-      case 4: launch_kc_step<4>(d_emb, n, ctx->kc_centre, upd, metric, d_mind, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
-      case 8: launch_kc_step<8>(d_emb, n, ctx->kc_centre, upd, metric, d_mind, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 1: launch_kc_step<1>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 2: launch_kc_step<2>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 4: launch_kc_step<4>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 8: launch_kc_step<8>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
     }
     kcenter_pick_kernel<<<1, 256, 0, st>>>(ctx->kc_part_val, ctx->kc_part_idx, blocks, d_emb, D, d_taken,
                                           ctx->kc_centre, (long long*)d_picks, d_pick_vals, step);

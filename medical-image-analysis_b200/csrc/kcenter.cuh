@@ -20,6 +20,7 @@
 namespace b200al {
 
 enum { METRIC_L2 = 0, METRIC_COSINE = 1 };
+enum { CRITERIA_MIN = 0, CRITERIA_MEAN = 1 };
 
 __device__ __forceinline__ double warp_sum_f64(double v) {
 #pragma unroll
@@ -128,6 +129,77 @@ kcenter_step_kernel(const float* __restrict__ emb, int n, const float* __restric
       if (lane == 0) mind[row] = m;
     }
     if (!taken[row] && (m > bv)) { bv = m; bi = row; }  // rows ascend: strict > keeps the first max
+  }
+  __shared__ float sv[32];
+  __shared__ int si[32];
+  if (lane == 0) { sv[warp] = bv; si[warp] = bi; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    for (int w = 1; w < nw; ++w)
+      if (sv[w] > bv || (sv[w] == bv && si[w] < bi)) { bv = sv[w]; bi = si[w]; }
+    part_val[blockIdx.x] = bv;
+    part_idx[blockIdx.x] = bi;
+  }
+}
+
+// ---- coreset_criteria == "mean" (coreset_selector.py:35-36): the score of an unlabeled row is the MEAN
+// distance to all current centres.  Kept as a running fp64 sum per row (the reference re-averages an fp32
+// matrix slice every step); the divisor is the same for every row, so it only scales the reported value.
+template <int NV, int ROWS>
+__global__ void __launch_bounds__(256)
+kcenter_init_mean_kernel(const float* __restrict__ emb, int n, const float* __restrict__ centres, int L, int metric,
+                         double* __restrict__ msum, int accumulate) {
+  const int lane = threadIdx.x & 31;
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  constexpr int D = NV * 128;
+  for (int r0 = warp_global * ROWS; r0 < n; r0 += nwarps * ROWS) {
+    float4 x[ROWS][NV];
+    double sum[ROWS];
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      const int row = min(r0 + r, n - 1);
+      load_row<NV>(emb + (size_t)row * D, lane, x[r]);
+      sum[r] = accumulate ? msum[row] : 0.0;
+    }
+    for (int j = 0; j < L; ++j) {
+      float4 c[NV];
+      load_row<NV>(centres + (size_t)j * D, lane, c);
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r) sum[r] += (double)row_distance<NV>(x[r], c, metric);
+    }
+    if (lane == 0) {
+#pragma unroll
+      for (int r = 0; r < ROWS; ++r)
+        if (r0 + r < n) msum[r0 + r] = sum[r];
+    }
+  }
+}
+
+template <int NV>
+__global__ void __launch_bounds__(256)
+kcenter_step_mean_kernel(const float* __restrict__ emb, int n, const float* __restrict__ centre, int do_update,
+                         int metric, double* __restrict__ msum, double inv_count, const uint8_t* __restrict__ taken,
+                         float* __restrict__ part_val, int* __restrict__ part_idx) {
+  constexpr int D = NV * 128;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  const int rows_per_block = (n + gridDim.x - 1) / gridDim.x;
+  const int r_begin = blockIdx.x * rows_per_block;
+  const int r_end = min(n, r_begin + rows_per_block);
+  float4 c[NV];
+  if (do_update) load_row<NV>(centre, lane, c);
+  float bv = -CUDART_INF_F;
+  int bi = 0x7fffffff;
+  for (int row = r_begin + warp; row < r_end; row += nw) {
+    double m = msum[row];
+    if (do_update) {
+      float4 x[NV];
+      load_row<NV>(emb + (size_t)row * D, lane, x);
+      m += (double)row_distance<NV>(x, c, metric);
+      if (lane == 0) msum[row] = m;
+    }
+    const float v = (float)(m * inv_count);
+    if (!taken[row] && (v > bv)) { bv = v; bi = row; }
   }
   __shared__ float sv[32];
   __shared__ int si[32];

@@ -120,9 +120,9 @@ def cosine_rows(feats_n: np.ndarray, centre_n: np.ndarray, self_index: int | Non
 # ---------------------------------------------------------------------------
 # k-center greedy
 # ---------------------------------------------------------------------------
-def kcenter_greedy_matrix(dist_mat: np.ndarray, budget: int, init_idx) -> list[int]:
-    """coreset_selector.py:19-51 (criteria "min") restated on a full distance
-    matrix, returning the picks IN SELECTION ORDER (the reference returns
+def kcenter_greedy_matrix(dist_mat: np.ndarray, budget: int, init_idx, criteria: str = "min") -> list[int]:
+    """coreset_selector.py:19-51 restated on a full distance matrix, returning
+    the picks IN SELECTION ORDER (the reference returns
     `list(set(selected) - set(init_idx))`, order lost - line 49)."""
     n = dist_mat.shape[0]
     labeled = np.zeros(n, dtype=bool)
@@ -130,11 +130,41 @@ def kcenter_greedy_matrix(dist_mat: np.ndarray, budget: int, init_idx) -> list[i
     picks = []
     for _ in range(budget):
         sub = dist_mat[~labeled][:, labeled]             # :31
-        nearest = sub.min(axis=1)                        # :34
+        nearest = sub.min(axis=1) if criteria == "min" else sub.mean(axis=1)   # :34 / :36
         q = np.arange(n)[~labeled][nearest.argmax()]     # :43-44 (first max)
         labeled[q] = True                                # :45
         picks.append(int(q))
     return picks
+
+
+def kcenter_greedy_mean_stream(feats: np.ndarray, n_init: int, budget: int, metric: str = "l2",
+                               return_gaps: bool = False):
+    """criteria "mean" (coreset_selector.py:35-36) without the N x N matrix: the
+    score of an unlabeled row is its mean distance to all current centres, kept
+    as a running fp64 sum of the fp32 distances (the reference averages an fp32
+    matrix slice with numpy's pairwise fp32 summation, so the two agree to fp32
+    rounding of the mean; `return_gaps` exposes the top-2 margin per step)."""
+    feats = np.ascontiguousarray(feats, dtype=np.float32)
+    n = feats.shape[0]
+    fn, f = (l2_rows, feats) if metric == "l2" else (cosine_rows, normalize_rows(feats))
+    msum = np.zeros(n, dtype=np.float64)
+    for j in range(n_init):
+        msum += fn(f, f[j], j).astype(np.float64)
+    taken = np.zeros(n, dtype=bool)
+    taken[:n_init] = True
+    picks, gaps = [], []
+    for step in range(budget):
+        mean = (msum / float(n_init + step)).astype(np.float32)
+        cand = np.where(taken, -np.inf, mean)
+        q = int(cand.argmax())
+        if return_gaps:
+            top = cand[q]
+            cand[q] = -np.inf
+            gaps.append(float(top - cand.max()) if n - taken.sum() > 1 else float("inf"))
+        taken[q] = True
+        picks.append(q)
+        msum += fn(f, f[q], q).astype(np.float64)
+    return (picks, gaps) if return_gaps else picks
 
 
 def kcenter_greedy_stream(feats: np.ndarray, n_init: int, budget: int, metric: str = "l2",

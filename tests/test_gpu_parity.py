@@ -144,6 +144,32 @@ def test_kcenter_random_features_exact():
     eng.close()
 
 
+def test_kcenter_mean_criteria_matches_oracle():
+    """coreset_criteria='mean' (coreset_selector.py:35-36): the running-sum kernel picks the oracle's rows
+    whenever the oracle's own top-2 margin is above fp32 rounding of the mean."""
+    import b200al
+    from oracle import select_ref as S
+    eng = b200al.Engine(DEV, 2, max_samples=1)
+    rng = np.random.default_rng(21)
+    checked = 0
+    for D, n, L, k in ((512, 3000, 40, 60), (256, 800, 3, 30)):
+        feats = (rng.standard_normal((n, D)) * 0.3 + 0.1).astype(np.float32)
+        for metric in ("l2", "cosine"):
+            want, gaps = S.kcenter_greedy_mean_stream(feats, L, k, metric, return_gaps=True)
+            got, vals = eng.kcenter(torch.from_numpy(feats).to(DEV), L, k, metric, return_vals=True, criteria="mean")
+            got = got.cpu().tolist()
+            # compare up to the first step whose margin is within rounding noise (after it the cascades may differ)
+            tol = 4e-7 * float(np.abs(vals.cpu().numpy()).max())
+            upto = next((i for i, g in enumerate(gaps) if g <= tol), k)
+            assert got[:upto] == want[:upto], (D, metric, upto)
+            checked += upto
+            assert len(set(got)) == k and min(got) >= L
+    assert checked > 100
+    with pytest.raises(RuntimeError):
+        eng.kcenter(torch.from_numpy(feats).to(DEV), L, 3, "l2", criteria="median")
+    eng.close()
+
+
 def test_topk_exact_with_ties():
     import b200al
     from oracle.select_ref import rank_desc_stable

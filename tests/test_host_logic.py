@@ -84,8 +84,7 @@ def test_selector_ctor_contract():
     s = b200al.B200EntropySelector(batch_size=12, num_workers=1, pin_memory=False)
     assert isinstance(s, b200al.ActiveSelector) and s.mode == "entropy"
     assert b200al.B200MCDropoutEntropySelector(8, 0).mc_repeats == 8
-    with pytest.raises(NotImplementedError):
-        b200al.B200CoresetSelector(8, 0, coreset_criteria="mean")
+    assert b200al.B200CoresetSelector(8, 0, coreset_criteria="mean").coreset_criteria == "mean"
     with pytest.raises(RuntimeError, match="undefined"):   # coreset_selector.py:38-40
         b200al.B200CoresetSelector(8, 0, coreset_criteria="median")
     with pytest.raises(NotImplementedError):

@@ -84,6 +84,12 @@ def test_kcenter_restatements_equal_reference(ref):
         # the reference's /sum normalisation (coreset_selector.py:153) does not change the picks
         d2 = dist / dist.sum()
         assert sorted(int(i) for i in ref.kcenter_greedy(d2, 500, 40, np.arange(25), "min")) == sorted(int(i) for i in want)
+        # criteria "mean" (coreset_selector.py:35-36): matrix restatement and the running-sum form
+        want_m = sorted(int(i) for i in ref.kcenter_greedy(dist, 500, 40, np.arange(25), "mean"))
+        assert sorted(S.kcenter_greedy_matrix(dist, 40, np.arange(25), "mean")) == want_m
+        got_m, gaps = S.kcenter_greedy_mean_stream(feats, 25, 40, metric, return_gaps=True)
+        if min(gaps) > 1e-5 * float(dist.mean()):   # no fp32-rounding-level tie between the two best rows
+            assert sorted(got_m) == want_m
     col = S.l2_rows(feats, feats[7], 7)
     np.testing.assert_array_equal(col, pairwise_distances(feats, metric="l2")[:, 7])
 
