@@ -5,7 +5,8 @@ selector by `config.active_selector_name` and raises ValueError for unknown
 names.  `install_into_al_trainer(ALTrainer)` wraps that method so the names in
 `b200al.SELECTORS` ("b200-entropy", "b200-coreset-l2", ...) construct the
 B200 selectors with the same kwargs the reference passes (batch_size,
-num_workers, pin_memory); every other name goes to the original method.
+num_workers, pin_memory, and coreset_criteria / coreset_fusion for the coreset
+names); every other name goes to the original method.
 """
 from __future__ import annotations
 
@@ -18,11 +19,15 @@ def install_into_al_trainer(trainer_cls, reference_abc=None):
     def _setup_active_selector(self):
         name = self.config.active_selector_name
         if name in SELECTORS:
-            self.active_selector = SELECTORS[name](
+            kw = dict(
                 batch_size=self.config.batch_size,
                 num_workers=self.config.num_workers,
                 pin_memory=self.config.pin_memory,
             )
+            if name.startswith("b200-coreset"):  # al_trainer.py:823-844 forwards these two to CoresetSelector
+                kw["coreset_criteria"] = getattr(self.config, "coreset_criteria", "min")
+                kw["coreset_fusion"] = getattr(self.config, "coreset_fusion", "add")
+            self.active_selector = SELECTORS[name](**kw)
         else:
             original(self)
 

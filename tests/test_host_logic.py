@@ -147,6 +147,11 @@ def test_install_into_al_trainer_shim():
     t = Trainer()
     t._setup_active_selector()
     assert isinstance(t.active_selector, b200al.B200MarginSelector) and t.active_selector.batch_size == 12
+    t.config.active_selector_name = "b200-coreset-l2"   # al_trainer.py:823-833 forwards the coreset options
+    t.config.coreset_criteria = "mean"
+    t._setup_active_selector()
+    assert isinstance(t.active_selector, b200al.B200CoresetSelector)
+    assert (t.active_selector.metric, t.active_selector.coreset_criteria) == ("l2", "mean")
     t.config.active_selector_name = "nope"
     with pytest.raises(ValueError):
         t._setup_active_selector()
