@@ -88,20 +88,34 @@ const char* b200al_last_error(const b200al_ctx* ctx); /* ctx may be NULL: last g
  * Replaces reading `model.state_dict()` each round (al_trainer.py:1048-1083). */
 int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, void* stream);
 
+/* Pool-image input pipeline (the dataset side of the reference: FUGCDataset.get_sample fugc_dataset.py:140-160 /
+ * BUSIDataset.get_sample busi_dataset.py:126-143 -> F.to_tensor -> JointResize joint_transform.py:20-25 ->
+ * ZScoreNormalize normalization.py:13-21) for n grayscale uint8 images of ragged sizes held in one device buffer:
+ * image i = d_raw + d_offsets[i], d_hw[2i] rows x d_hw[2i+1] columns, tightly packed.  max_h / max_w bound the
+ * source sizes (they size the antialias filter tables; down-scale factors up to 17 are supported).
+ * d_images_out [n,H,W] fp32 = u8/255 resized with torch's antialiased bilinear filter.
+ * d_norm_out nullable [n][2] = per-image (mean, unbiased std clipped at 1e-8) of the resized image; hand it to
+ * b200al_unet_scores / b200al_unet_embed as d_norm to apply ZScoreNormalize inside the first conv's loader. */
+int b200al_prep_images(b200al_ctx* ctx, const uint8_t* d_raw, const int64_t* d_offsets, const int32_t* d_hw, int n,
+                       int max_h, int max_w, float* d_images_out, float* d_norm_out, void* stream);
+
 /* Score n pool images: UNet.forward (unet.py:293) + the selector's per-image
  * score, T >= 1 MC-dropout repeats (T == 1 and drop_p == 0: plain eval mode,
  * exactly the reference selectors).  d_images: [n,H,W] u8 or f32.
+ * d_norm nullable [n][2]: per-image (mean, std); pixels become (x - mean) / std on load (ZScoreNormalize,
+ * normalization.py:21; --do-normalize), zero padding stays zero.
  * MC masks: d_drop_masks ([n,T,2944] multipliers, 0 or 1/(1-p)) if non-NULL,
  * else generated from (mc_seed, base_pos + i, t, channel) - see oracle/synth.py.
  * d_scores_out [n] fp32.  d_logits_out nullable: [n*T, K, H, W] fp32.
  * n*T must be <= max_samples. */
-int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int image_dtype, int n, int mode, int T, float drop_p,
-                       uint64_t mc_seed, int64_t base_pos, const float* d_drop_masks, float smooth,
-                       float* d_scores_out, float* d_logits_out, void* stream);
+int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int image_dtype, const float* d_norm, int n, int mode,
+                       int T, float drop_p, uint64_t mc_seed, int64_t base_pos, const float* d_drop_masks,
+                       float smooth, float* d_scores_out, float* d_logits_out, void* stream);
 
 /* UNet.get_enc_feature (unet.py:296-297, 89-93): encoder + global average pool.
  * d_emb_out [n,512] fp32.  n <= max_samples. */
-int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, int n, float* d_emb_out, void* stream);
+int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, const float* d_norm, int n,
+                      float* d_emb_out, void* stream);
 
 /* Kernel 3 alone: scores from fp32 logits [n,T,K,HW] already in HBM
  * (softmax -> mean over T -> entropy / margin / confidence -> mean over pixels). */

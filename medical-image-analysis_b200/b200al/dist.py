@@ -70,3 +70,21 @@ def global_topk(local_scores: torch.Tensor, local_pos: torch.Tensor, k: int, gro
 def gather_rows(local_rows: torch.Tensor, group=None) -> torch.Tensor:
     """All ranks' rows in rank (== pool position) order."""
     return all_gather_varlen(local_rows, group)
+
+
+def broadcast_state_dict(sd: dict, device, src: int = 0, group=None) -> dict:
+    """Rank `src`'s floating-point tensors of `sd` on every rank (one flat fp32 broadcast), so that all ranks score
+    their shard with the same weights even if their trainers drifted; non-float entries (num_batches_tracked) are
+    kept local.  The reference reloads / rebuilds the model before each selection (al_trainer.py:1048-1083)."""
+    rank, ws = world()
+    if ws == 1:
+        return sd
+    names = [k for k, v in sd.items() if torch.is_tensor(v) and v.is_floating_point()]
+    flat = torch.cat([sd[k].detach().to(device=device, dtype=torch.float32).reshape(-1) for k in names])
+    dist.broadcast(flat, src=src, group=group)
+    out, off = dict(sd), 0
+    for k in names:
+        n = sd[k].numel()
+        out[k] = flat[off:off + n].view(sd[k].shape)
+        off += n
+    return out

@@ -130,10 +130,12 @@ class Engine:
         _lib.check(rc, self.ctx)
 
     # ---------------------------------------------------------------- weights
-    def load_model(self, model) -> None:
+    def load_model(self, model, state_dict=None) -> None:
         """Fold + pack the weights of `model` (nn.Module with the reference
-        UNet's state_dict layout, or a plain state_dict)."""
-        sd = model.state_dict() if hasattr(model, "state_dict") else model
+        UNet's state_dict layout, or a plain state_dict).  `state_dict` overrides
+        the tensors (e.g. the copy broadcast from rank 0); hyper-parameters still
+        come from `model`."""
+        sd = state_dict if state_dict is not None else (model.state_dict() if hasattr(model, "state_dict") else model)
         K = validate_state_dict(sd)
         if K != self.K:
             raise ValueError(f"model has {K} output classes, engine was created for {self.K}")
@@ -181,13 +183,42 @@ class Engine:
             return images.contiguous(), _lib.F32
         raise TypeError(f"image dtype {images.dtype} not supported (uint8 or float32)")
 
+    def _norm(self, norm, n: int):
+        if norm is None:
+            return None
+        norm = norm.to(device=self.device, dtype=torch.float32).contiguous()
+        if tuple(norm.shape) != (n, 2):
+            raise ValueError("norm must be [n,2] = per-image (mean, std)")
+        return norm
+
+    def prep(self, raw: torch.Tensor, offsets: torch.Tensor, hw: torch.Tensor, max_h: int, max_w: int,
+             normalize: bool = False):
+        """Dataset-side pipeline on the device (to_tensor -> JointResize -> ZScoreNormalize statistics) for n ragged
+        grayscale uint8 images packed in `raw` (uint8 [bytes]); offsets int64 [n], hw int32 [n,2], all on device.
+        Returns (images fp32 [n,H,W], norm [n,2] or None); pass `norm` on to scores / embed."""
+        n = int(offsets.shape[0])
+        for t, dt in ((raw, torch.uint8), (offsets, torch.int64), (hw, torch.int32)):
+            if t.device != self.device or t.dtype != dt or not t.is_contiguous():
+                raise ValueError("prep: raw uint8 / offsets int64 / hw int32 must be contiguous on the engine's device")
+        if tuple(hw.shape) != (n, 2):
+            raise ValueError("hw must be [n,2]")
+        out = torch.empty((n, self.H, self.W), dtype=torch.float32, device=self.device)
+        norm = torch.empty((n, 2), dtype=torch.float32, device=self.device) if normalize else None
+        with torch.cuda.device(self.device):
+            self._check(self.lib.b200al_prep_images(self.ctx, self._ptr(raw), self._ptr(offsets), self._ptr(hw), n,
+                                                    int(max_h), int(max_w), self._ptr(out), self._ptr(norm),
+                                                    self._stream()))
+        return out, norm
+
     def scores(self, images: torch.Tensor, mode: str = "entropy", T: int = 1, drop_p: float = 0.0, seed: int = 0,
                base_pos: int = 0, masks: torch.Tensor | None = None, smooth: float = 1e-8,
-               return_logits: bool = False):
+               return_logits: bool = False, norm: torch.Tensor | None = None):
         """Per-image scores [n] (fp32, on device) for device-resident images
-        [n,H,W] / [n,1,H,W]; chunks internally to max_samples // T images."""
+        [n,H,W] / [n,1,H,W]; chunks internally to max_samples // T images.
+        norm: optional [n,2] per-image (mean, std) -> ZScoreNormalize applied while loading."""
         imgs, dt = self._images(images)
         n = imgs.shape[0]
+        norm = self._norm(norm, n)
         out = torch.empty(n, dtype=torch.float32, device=self.device)
         logits = torch.empty((n * T, self.K, self.H, self.W), dtype=torch.float32, device=self.device) \
             if return_logits else None
@@ -203,21 +234,24 @@ class Engine:
             for i in range(0, n, per):
                 m = min(per, n - i)
                 self._check(self.lib.b200al_unet_scores(
-                    self.ctx, self._ptr(imgs[i:i + m]), dt, m, _lib.MODES[mode], T, float(drop_p), int(seed),
+                    self.ctx, self._ptr(imgs[i:i + m]), dt, self._ptr(norm[i:i + m] if norm is not None else None), m,
+                    _lib.MODES[mode], T, float(drop_p), int(seed),
                     int(base_pos + i), self._ptr(masks[i:i + m] if masks is not None else None), float(smooth),
                     self._ptr(out[i:i + m]), self._ptr(logits[i * T:(i + m) * T] if logits is not None else None), st))
         return (out, logits) if return_logits else out
 
-    def embed(self, images: torch.Tensor) -> torch.Tensor:
+    def embed(self, images: torch.Tensor, norm: torch.Tensor | None = None) -> torch.Tensor:
         """UNet.get_enc_feature: [n,512] fp32 on device."""
         imgs, dt = self._images(images)
         n = imgs.shape[0]
+        norm = self._norm(norm, n)
         out = torch.empty((n, _lib.EMBED_DIM), dtype=torch.float32, device=self.device)
         st = self._stream()
         with torch.cuda.device(self.device):
             for i in range(0, n, self.max_samples):
                 m = min(self.max_samples, n - i)
-                self._check(self.lib.b200al_unet_embed(self.ctx, self._ptr(imgs[i:i + m]), dt, m,
+                self._check(self.lib.b200al_unet_embed(self.ctx, self._ptr(imgs[i:i + m]), dt,
+                                                       self._ptr(norm[i:i + m] if norm is not None else None), m,
                                                        self._ptr(out[i:i + m]), st))
         return out
 

@@ -10,12 +10,22 @@ device and maps positions back to case names.
 Objects consumed (duck-typed, reference types or mirrors): `active_dataset`
 with get_size / get_pool_dataset / get_train_dataset; datasets with
 `.image_idx: list[str]` and `__getitem__ -> {"image": float32 [1,H,W], ...}`.
-Fast path: if the wrapped base dataset exposes `images_u8` ([N,H,W] uint8
-tensor, CPU or CUDA) and `names`, chunks are sliced from it directly instead of
-going through a DataLoader.
+Fast paths: (1) if the wrapped base dataset exposes `images_u8` ([N,H,W] uint8
+tensor, CPU or CUDA) and `names`, chunks are sliced from it directly; (2) for
+datasets whose raw pixels can be read (pool_cache.py: the reference's FUGC /
+BUSI datasets, or anything with `b200_raw_u8`) the raw bytes are cached in HBM
+once per run and resize + z-score run on the GPU.  Otherwise a DataLoader with
+the reference's settings feeds fp32 batches.
+
+Every `select_next_batch` leaves `self.last_timing` (seconds, pool size,
+images/s) and logs it on the "b200al" logger - the reference's trainer times
+epochs and iterations but not acquisition (al_trainer.py:1148-1202).
 """
 from __future__ import annotations
 
+import functools
+import logging
+import time
 from abc import ABC, abstractmethod
 from typing import Any, Iterator
 
@@ -23,6 +33,9 @@ import torch
 
 from . import dist as D
 from .engine import Engine, validate_state_dict
+from .pool_cache import pool_cache_for
+
+log = logging.getLogger("b200al")
 
 
 class ActiveSelector(ABC):
@@ -58,32 +71,46 @@ def _cold_start(active_dataset, select_num: int) -> list:
 class PoolSource:
     """Feeds device-resident image chunks of a dataset in position order."""
 
-    def __init__(self, dataset, device, batch_size: int, num_workers: int, pin_memory: bool):
+    def __init__(self, dataset, device, batch_size: int, num_workers: int, pin_memory: bool, pool_cache: str = "auto"):
         self.ds, self.device = dataset, torch.device(device)
         self.batch_size, self.num_workers, self.pin_memory = batch_size, num_workers, pin_memory
         base = getattr(dataset, "dataset", None)
         self.resident = None
-        if base is not None and hasattr(base, "images_u8") and hasattr(dataset, "case_name_to_idx"):
-            self.resident = base.images_u8
+        self.cache = None
+        if base is not None and hasattr(dataset, "case_name_to_idx"):
+            if hasattr(base, "images_u8"):
+                self.resident = base.images_u8
+            else:
+                self.cache = pool_cache_for(base, self.device, pool_cache)
 
     def image_hw(self) -> tuple[int, int]:
         if self.resident is not None:
             return tuple(self.resident.shape[-2:])
+        if self.cache is not None:
+            return self.cache.out_hw
         if len(self.ds) == 0:
             return (256, 256)
         return tuple(self.ds[0]["image"].shape[-2:])
 
-    def chunks(self, positions: list[int], chunk: int) -> Iterator[tuple[int, torch.Tensor]]:
-        """Yields (offset into `positions`, images on device) with one chunk of
+    def chunks(self, positions: list[int], chunk: int, eng: Engine | None = None
+               ) -> Iterator[tuple[int, torch.Tensor, torch.Tensor | None]]:
+        """Yields (offset into `positions`, images on device, per-image (mean, std) or None) with one chunk of
         host->device copy in flight ahead of the consumer."""
         if not positions:
+            return
+        if self.cache is not None:
+            rows = torch.tensor([self.ds.case_name_to_idx[self.ds.image_idx[p]] for p in positions], dtype=torch.int64,
+                                device=self.cache.device)
+            for i in range(0, len(positions), chunk):
+                imgs, norm = self.cache.gather(eng, rows[i:i + chunk])
+                yield i, imgs, norm
             return
         if self.resident is not None:
             rows = torch.tensor([self.ds.case_name_to_idx[self.ds.image_idx[p]] for p in positions], dtype=torch.int64)
             if self.resident.is_cuda:
                 rows = rows.to(self.resident.device)
                 for i in range(0, len(positions), chunk):
-                    yield i, self.resident.index_select(0, rows[i:i + chunk]).to(self.device)
+                    yield i, self.resident.index_select(0, rows[i:i + chunk]).to(self.device), None
                 return
             copy_stream = torch.cuda.Stream(self.device)
             cur = torch.cuda.current_stream(self.device)
@@ -109,7 +136,7 @@ class PoolSource:
                     nxt = stage(i + chunk)
                 cur.wait_event(ev)
                 dev.record_stream(cur)
-                yield i, dev
+                yield i, dev, None
             return
         # generic path: the reference's own DataLoader settings (entropy_selector.py:30-35)
         from torch.utils.data import DataLoader, Subset
@@ -118,24 +145,61 @@ class PoolSource:
         off = 0
         for batch in loader:
             img = batch["image"].to(self.device, non_blocking=True).to(torch.float32)
-            yield off, img
+            yield off, img, None
             off += img.shape[0]
+
+
+def _timed(fn):
+    @functools.wraps(fn)
+    def wrapper(self, active_dataset, select_num, model, device):
+        dev = torch.device(device)
+        t0 = time.perf_counter()
+        out = fn(self, active_dataset, select_num, model, device)
+        if dev.type == "cuda":
+            torch.cuda.synchronize(dev)
+        dt = time.perf_counter() - t0
+        labeled, pool = active_dataset.get_size()
+        self.last_timing = {"seconds": dt, "pool": pool, "labeled": labeled, "selected": len(out),
+                            "images_per_s": pool / dt if dt > 0 else float("inf")}
+        log.info("%s: %d of %d pool images selected in %.3f s (%.0f images/s, %d labeled)", type(self).__name__,
+                 len(out), pool, dt, self.last_timing["images_per_s"], labeled)
+        return out
+
+    return wrapper
 
 
 class _B200Base(ActiveSelector):
     def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8, *,
-                 precision: str = "bf16x3", chunk_samples: int = 64):
+                 precision: str = "bf16x3", chunk_samples: int = 64, pool_cache: str = "auto",
+                 sync_weights: bool = True):
         self.batch_size, self.num_workers, self.pin_memory = batch_size, num_workers, pin_memory
         self.smooth = smooth
         self.precision = precision
         self.chunk_samples = chunk_samples
+        if pool_cache not in ("auto", "off"):
+            raise ValueError("pool_cache must be 'auto' or 'off'")
+        self.pool_cache = pool_cache
+        self.sync_weights = bool(sync_weights)  # multi-GPU: every rank scores with rank 0's weights
+        self.last_timing: dict | None = None
+
+    def __init_subclass__(cls, **kw):
+        super().__init_subclass__(**kw)
+        if "select_next_batch" in cls.__dict__:  # acquisition-time logging for every concrete selector
+            cls.select_next_batch = _timed(cls.__dict__["select_next_batch"])
+
+    def _source(self, dataset, device) -> "PoolSource":
+        return PoolSource(dataset, device, self.batch_size, self.num_workers, self.pin_memory, self.pool_cache)
 
     def _engine(self, model, device, hw) -> Engine:
         sd = model.state_dict()
         K = validate_state_dict(sd)
         eng = get_engine(device, K, hw[0], hw[1], self.precision, self.chunk_samples)
         model.eval()  # the reference's own side effect (entropy_selector.py:42)
-        eng.load_model(model)  # every call: the trainer rebuilds / reloads the model each round
+        # every call: the trainer rebuilds / reloads the model each round (al_trainer.py:1048-1083)
+        if self.sync_weights and D.world()[1] > 1:
+            eng.load_model(model, D.broadcast_state_dict(sd, eng.device))
+        else:
+            eng.load_model(model)
         return eng
 
 
@@ -154,17 +218,17 @@ class _B200Uncertainty(_B200Base):
             p = self.dropout_prob if self.dropout_prob is not None else (eng.dropout_p or 0.0)
         out = torch.empty(len(positions), dtype=torch.float32, device=eng.device)
         per = max(1, eng.max_samples // T)
-        for off, imgs in src.chunks(positions, per):
+        for off, imgs, norm in src.chunks(positions, per, eng):
             # MC masks are keyed by pool position so any sharding gives the same scores
             out[off:off + imgs.shape[0]] = eng.scores(imgs, self.mode, T=T, drop_p=p, seed=self.mc_seed,
-                                                      base_pos=positions[off], smooth=self.smooth)
+                                                      base_pos=positions[off], smooth=self.smooth, norm=norm)
         return out
 
     def _scores_local(self, active_dataset, model, device):
         pool = active_dataset.get_pool_dataset()
         rank, ws = D.world()
         lo, hi = D.shard_range(len(pool), rank, ws)
-        src = PoolSource(pool, device, self.batch_size, self.num_workers, self.pin_memory)
+        src = self._source(pool, device)
         eng = self._engine(model, device, src.image_hw())
         return eng, self._score_positions(eng, src, list(range(lo, hi))), lo, hi
 
@@ -214,8 +278,8 @@ class B200MCDropoutEntropySelector(_B200Uncertainty):
 
 def _embed_positions(eng: Engine, src: PoolSource, positions: list[int]) -> torch.Tensor:
     out = torch.empty((len(positions), 512), dtype=torch.float32, device=eng.device)
-    for off, imgs in src.chunks(positions, eng.max_samples):
-        out[off:off + imgs.shape[0]] = eng.embed(imgs)
+    for off, imgs, norm in src.chunks(positions, eng.max_samples, eng):
+        out[off:off + imgs.shape[0]] = eng.embed(imgs, norm=norm)
     return out
 
 
@@ -244,8 +308,8 @@ class B200CoresetSelector(_B200Base):
         all_list = list(labeled.image_idx) + list(pool.image_idx)  # labeled rows first (coreset_selector.py:85-88)
         rank, ws = D.world()
         lo, hi = D.shard_range(pool_size, rank, ws)
-        psrc = PoolSource(pool, device, self.batch_size, self.num_workers, self.pin_memory)
-        lsrc = PoolSource(labeled, device, self.batch_size, self.num_workers, self.pin_memory)
+        psrc = self._source(pool, device)
+        lsrc = self._source(labeled, device)
         eng = self._engine(model, device, psrc.image_hw())
         emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
         emb_p = D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi))))
@@ -272,8 +336,8 @@ class B200HybridSelector(_B200Uncertainty):
         labeled, pool = active_dataset.get_train_dataset(), active_dataset.get_pool_dataset()
         rank, ws = D.world()
         lo, hi = D.shard_range(pool_size, rank, ws)
-        psrc = PoolSource(pool, device, self.batch_size, self.num_workers, self.pin_memory)
-        lsrc = PoolSource(labeled, device, self.batch_size, self.num_workers, self.pin_memory)
+        psrc = self._source(pool, device)
+        lsrc = self._source(labeled, device)
         eng = self._engine(model, device, psrc.image_hw())
         scores = self._score_positions(eng, psrc, list(range(lo, hi)))
         m = min(pool_size, self.prefilter_factor * select_num)

@@ -17,6 +17,7 @@
 #include "conv_fold.cuh"
 #include "conv_tc.cuh"
 #include "kcenter.cuh"
+#include "prep.cuh"
 #include "topk.cuh"
 #include "uncertainty.cuh"
 #include "unet_misc.cuh"
@@ -91,6 +92,7 @@ struct b200al_ctx {
   bool fuse_head = false;
   double* partial = nullptr;
   int partial_blocks = 0;
+  double* prep_partials = nullptr;  // [max_samples][ceil(H / kPrepBand)][2] z-score partial sums
   float slope = 0.01f;
   // k-center / top-k scratch
   float *kc_part_val = nullptr, *kc_centre = nullptr;
@@ -649,6 +651,7 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
   TRY_RC(dev_alloc(ctx, &ctx->mask, (size_t)max_samples * B200AL_MASK_CHANNELS));
   ctx->partial_blocks = 64;
   TRY_RC(dev_alloc(ctx, &ctx->partial, (size_t)max_samples * ctx->partial_blocks));
+  TRY_RC(dev_alloc(ctx, &ctx->prep_partials, (size_t)max_samples * ((ctx->H + kPrepBand - 1) / kPrepBand) * 2));
   ctx->kc_blocks = ctx->sm_count * 4;
   TRY_RC(dev_alloc(ctx, &ctx->kc_part_val, (size_t)ctx->kc_blocks));
   TRY_RC(dev_alloc(ctx, &ctx->kc_part_idx, (size_t)ctx->kc_blocks));
@@ -741,19 +744,21 @@ extern "C" int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, voi
 namespace {
 
 // first conv over n images, each expanded to T samples (sample = image * T + t); mask nullable [n*T][2944]
-int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, int n, int T, const float* mask, cudaStream_t st) {
+// norm nullable [n][2] = per-image (mean, std) of the fused ZScoreNormalize
+int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, const float* norm, int n, int T, const float* mask,
+                   cudaStream_t st) {
   dim3 grid((ctx->W + 255) / 256, ctx->H, n);
   const ActBuf& ob = ctx->bufs[E0A];
   const size_t smem = (size_t)T * 64 * sizeof(float);
   if (smem > 48 * 1024) return set_err(ctx, B200AL_ERR_ARG, "T = %d too large", T);
   if (dtype == B200AL_U8)
-    conv_first_kernel<uint8_t><<<grid, 256, smem, st>>>((const uint8_t*)d_images, T, ctx->H, ctx->W, ctx->first_consts,
-                                                       mask, B200AL_MASK_CHANNELS, ctx->slope, ob.ptr, 2 * ob.c_total,
-                                                       0, ob.c_total, ctx->nsplit == 3);
+    conv_first_kernel<uint8_t><<<grid, 256, smem, st>>>((const uint8_t*)d_images, norm, T, ctx->H, ctx->W,
+                                                       ctx->first_consts, mask, B200AL_MASK_CHANNELS, ctx->slope,
+                                                       ob.ptr, 2 * ob.c_total, 0, ob.c_total, ctx->nsplit == 3);
   else if (dtype == B200AL_F32)
-    conv_first_kernel<float><<<grid, 256, smem, st>>>((const float*)d_images, T, ctx->H, ctx->W, ctx->first_consts, mask,
-                                                     B200AL_MASK_CHANNELS, ctx->slope, ob.ptr, 2 * ob.c_total, 0,
-                                                     ob.c_total, ctx->nsplit == 3);
+    conv_first_kernel<float><<<grid, 256, smem, st>>>((const float*)d_images, norm, T, ctx->H, ctx->W,
+                                                     ctx->first_consts, mask, B200AL_MASK_CHANNELS, ctx->slope, ob.ptr,
+                                                     2 * ob.c_total, 0, ob.c_total, ctx->nsplit == 3);
   else
     return set_err(ctx, B200AL_ERR_ARG, "bad image dtype %d", dtype);
   ctx->launches++;
@@ -822,7 +827,43 @@ void launch_unc(const float* logits, int n, int T, int HW, int mode, float smoot
 
 }  // namespace
 
-extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int image_dtype, int n, int mode, int T,
+extern "C" int b200al_prep_images(b200al_ctx* ctx, const uint8_t* d_raw, const int64_t* d_offsets, const int32_t* d_hw,
+                                  int n, int max_h, int max_w, float* d_images_out, float* d_norm_out, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (n == 0) return B200AL_OK;
+  if (!d_raw || !d_offsets || !d_hw || !d_images_out || n < 0 || max_h < 1 || max_w < 1)
+    return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (ctx->W > 1024) return set_err(ctx, B200AL_ERR_ARG, "prep supports W <= 1024");
+  const float sc_h = (float)max_h / (float)ctx->H, sc_w = (float)max_w / (float)ctx->W;
+  const float sc = sc_h > sc_w ? sc_h : sc_w;
+  const int taps = 2 * (int)ceilf(sc > 1.f ? sc : 1.f) + 1;
+  if (taps > kPrepMaxTaps)
+    return set_err(ctx, B200AL_ERR_ARG, "source image %d x %d is more than 17x the model input", max_h, max_w);
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  const int bands = (ctx->H + kPrepBand - 1) / kPrepBand;
+  const size_t smem = ((size_t)taps * ctx->W + (size_t)kPrepBand * taps) * sizeof(float);
+  if (smem > 200 * 1024) return set_err(ctx, B200AL_ERR_ARG, "prep filter table does not fit shared memory");
+  static_assert(kPrepBand <= 32, "band rows are set up by the first warp");
+  CUDA_TRY(ctx, cudaFuncSetAttribute(prep_resize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  for (int i0 = 0; i0 < n; i0 += ctx->max_samples) {  // the partials buffer holds max_samples images
+    const int nn = (n - i0) < ctx->max_samples ? (n - i0) : ctx->max_samples;
+    double* part = d_norm_out ? ctx->prep_partials : nullptr;
+    prep_resize_kernel<<<dim3(bands, nn), ctx->W, smem, st>>>(d_raw, d_offsets + i0, d_hw + 2 * (size_t)i0, ctx->H,
+                                                              ctx->W, taps, d_images_out + (size_t)i0 * ctx->H * ctx->W,
+                                                              part);
+    ctx->launches++;
+    if (d_norm_out) {
+      prep_stats_kernel<<<(nn + 127) / 128, 128, 0, st>>>(part, bands, ctx->H * ctx->W, d_norm_out + 2 * (size_t)i0, nn);
+      ctx->launches++;
+    }
+  }
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int image_dtype, const float* d_norm, int n,
+                                  int mode, int T,
                                   float drop_p, uint64_t mc_seed, int64_t base_pos, const float* d_drop_masks,
                                   float smooth, float* d_scores_out, float* d_logits_out, void* stream) {
   if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
@@ -838,7 +879,7 @@ extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int ima
   int rc = prepare_masks(ctx, n, T, drop_p, mc_seed, base_pos, d_drop_masks, &mask, st);
   if (rc) return rc;
   const int S = n * T;
-  if ((rc = run_first_conv(ctx, d_images, image_dtype, n, T, mask, st))) return rc;
+  if ((rc = run_first_conv(ctx, d_images, image_dtype, d_norm, n, T, mask, st))) return rc;
   int nblk = ctx->partial_blocks;
   if (ctx->fuse_head) {
     // last decoder block + seg_output fused: logits [S][K][HW] fp32, then the HBM-bound softmax/score reduction
@@ -861,8 +902,8 @@ extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int ima
   return B200AL_OK;
 }
 
-extern "C" int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, int n, float* d_emb_out,
-                                 void* stream) {
+extern "C" int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, const float* d_norm, int n,
+                                 float* d_emb_out, void* stream) {
   if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
   if (!ctx->weights_loaded) return set_err(ctx, B200AL_ERR_STATE, "b200al_load_weights has not been called");
   if (n == 0) return B200AL_OK;
@@ -871,7 +912,7 @@ extern "C" int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int imag
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   int rc;
-  if ((rc = run_first_conv(ctx, d_images, image_dtype, n, 1, nullptr, st))) return rc;
+  if ((rc = run_first_conv(ctx, d_images, image_dtype, d_norm, n, 1, nullptr, st))) return rc;
   if ((rc = run_layers(ctx, kEncoderLayers, n, nullptr, st))) return rc;
   const ActBuf& bb = ctx->bufs[E4B];
   avgpool_kernel<<<n, 512, 0, st>>>(bb.ptr, (ctx->H >> 4) * (ctx->W >> 4), 2 * bb.c_total, 0, bb.c_total,

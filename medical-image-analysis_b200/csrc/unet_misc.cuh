@@ -97,7 +97,8 @@ struct FirstConvConsts {
 
 template <typename ImgT>
 __global__ void __launch_bounds__(256)
-conv_first_kernel(const ImgT* __restrict__ img, int T, int H, int W, const __grid_constant__ FirstConvConsts k,
+conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, int T, int H, int W,
+                  const __grid_constant__ FirstConvConsts k,
                   const float* __restrict__ mask, int mask_stride, float slope, __nv_bfloat16* __restrict__ out,
                   int out_pitch, int hi_off, int lo_off, int write_lo) {
   extern __shared__ float se[];  // [T][32] scale, then [T][32] shift
@@ -120,6 +121,9 @@ conv_first_kernel(const ImgT* __restrict__ img, int T, int H, int W, const __gri
   const int x0w = x - lane;
   const int y = blockIdx.y;
   const ImgT* im = img + (size_t)im_idx * H * W;
+  // ZScoreNormalize fused into the loader (normalization.py:21): (x - mean) / std on real pixels, padding stays 0
+  const float nm = norm ? norm[2 * im_idx] : 0.f;
+  const float nsd = norm ? norm[2 * im_idx + 1] : 1.f;
   float v[9];
 #pragma unroll
   for (int r = 0; r < 3; ++r)
@@ -130,6 +134,7 @@ conv_first_kernel(const ImgT* __restrict__ img, int T, int H, int W, const __gri
       if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
         if (sizeof(ImgT) == 1) t = (float)im[(size_t)yy * W + xx] / 255.0f;  // torchvision to_tensor
         else t = (float)im[(size_t)yy * W + xx];
+        if (norm) t = __fdiv_rn(t - nm, nsd);
       }
       v[r * 3 + c] = t;
     }

@@ -90,6 +90,8 @@ def load_reference() -> SimpleNamespace:
         ds = importlib.import_module("datasets")
         base = importlib.import_module("datasets.basedataset")
         cs = importlib.import_module("activelearning.coreset_selector")
+        norm = importlib.import_module("transforms.normalization")
+        jt = importlib.import_module("transforms.joint_transform")
     finally:
         sys.path.remove(REFERENCE_SRC)
     _cache = SimpleNamespace(
@@ -104,6 +106,10 @@ def load_reference() -> SimpleNamespace:
         ActiveDataset=ds.ActiveDataset,
         ExtendableDataset=ds.ExtendableDataset,
         BaseDataset=base.BaseDataset,
+        FUGCDataset=ds.FUGCDataset,
+        BUSIDataset=ds.BUSIDataset,
+        ZScoreNormalize=norm.ZScoreNormalize,
+        JointResize=jt.JointResize,
     )
     return _cache
 

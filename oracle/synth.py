@@ -67,6 +67,47 @@ class SynthBase(Dataset):
         return self.get_sample(index)
 
 
+class ZScoreNormalize:
+    """Marker mirror of the reference's transform (src/transforms/normalization.py:9); SynthRawBase applies the
+    oracle's restatement of it."""
+    target_dtype = torch.float32
+
+
+class SynthRawBase(Dataset):
+    """Stands in for FUGCDataset/BUSIDataset built the way `al_train` builds the POOL dataset
+    (al_trainer.py:623: transform=None, image_size=--image-size, normalize=ZScoreNormalize() under --do-normalize):
+    ragged grayscale uint8 "files"; `get_sample` runs the oracle's restatement of to_tensor -> JointResize ->
+    ZScoreNormalize on the CPU (oracle/prep_ref.py).  `b200_raw_u8` is the raw-pixel hook the device pool cache
+    reads instead."""
+
+    def __init__(self, raws: list, image_size=256, normalize: bool = False, names: list[str] | None = None):
+        self.raws = raws
+        self.names = names if names is not None else [case_name(i) for i in range(len(raws))]
+        self.image_size = image_size
+        self.normalize = ZScoreNormalize() if normalize else None
+        self.transform = None
+        self.image_channels = 1
+
+    def __len__(self):
+        return len(self.names)
+
+    def b200_raw_u8(self, index: int):
+        return self.raws[index]
+
+    def get_sample(self, index: int, normalize: bool = True):
+        from .prep_ref import prep_image
+        hw = (self.image_size, self.image_size) if isinstance(self.image_size, int) else tuple(self.image_size)
+        img = prep_image(self.raws[index], hw, self.normalize is not None and normalize)
+        return {
+            "image": torch.from_numpy(img).unsqueeze(0),
+            "label": torch.zeros(hw, dtype=torch.long),
+            "case_name": self.names[index],
+        }
+
+    def __getitem__(self, index):
+        return self.get_sample(index)
+
+
 class MirrorExtendable(Dataset):
     """Behavioural mirror of ExtendableDataset (src/datasets/common.py:12-40):
     a list of case names over a base dataset (without the reference's habit of

@@ -41,7 +41,33 @@ def test_sharded_topk_and_gather_world2(tmp_path):
     assert got["rows_equal"]
 
 
+def _bcast_worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        g = torch.Generator().manual_seed(100 + rank)  # every rank starts from DIFFERENT weights
+        sd = {"a.weight": torch.randn(3, 4, generator=g), "a.bias": torch.randn(3, generator=g),
+              "bn.num_batches_tracked": torch.tensor(7 + rank)}
+        got = D.broadcast_state_dict(sd, "cpu")
+        torch.save({k: v.clone() for k, v in got.items()}, f"{out}.{rank}")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_state_dict_broadcast_world2(tmp_path):
+    out = str(tmp_path / "sd")
+    mp.spawn(_bcast_worker, args=(2, 29519, out), nprocs=2, join=True)
+    r0, r1 = torch.load(f"{out}.0"), torch.load(f"{out}.1")
+    g = torch.Generator().manual_seed(100)
+    want_w, want_b = torch.randn(3, 4, generator=g), torch.randn(3, generator=g)
+    for r in (r0, r1):
+        assert torch.equal(r["a.weight"], want_w) and torch.equal(r["a.bias"], want_b)
+    assert int(r0["bn.num_batches_tracked"]) == 7 and int(r1["bn.num_batches_tracked"]) == 8  # non-float: local
+
+
 def test_single_process_passthrough():
     assert D.world() == (0, 1)
     t = torch.arange(5)
     assert D.all_gather_varlen(t) is t
+    sd = {"w": torch.ones(2)}
+    assert D.broadcast_state_dict(sd, "cpu") is sd

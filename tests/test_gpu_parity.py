@@ -265,7 +265,7 @@ def test_scores_are_chunk_invariant_and_deterministic(env):
         from b200al import _lib
         import ctypes as C
         out = torch.empty(6, device=DEV)
-        _lib.check(small.lib.b200al_unet_scores(small.ctx, C.c_void_p(pool.data_ptr()), 0, 6, 0, 1, 0.0, 0, 0, None,
+        _lib.check(small.lib.b200al_unet_scores(small.ctx, C.c_void_p(pool.data_ptr()), 0, None, 6, 0, 1, 0.0, 0, 0, None,
                                                 1e-8, C.c_void_p(out.data_ptr()), None, None), small.ctx)
     small.close()
 

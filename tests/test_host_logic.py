@@ -157,6 +157,43 @@ def test_install_into_al_trainer_shim():
         t._setup_active_selector()
 
 
+def test_pool_source_serves_cached_rows_in_pool_order():
+    """Host side of the device pool cache (ragged packing, name -> row mapping, chunking, cache reuse); the kernel
+    is replaced by a stand-in that unpacks the same buffers and runs the oracle pipeline."""
+    from b200al.selectors import PoolSource
+    from oracle.prep_ref import prep_image, synth_raw_u8
+    from oracle.synth import MirrorExtendable, SynthRawBase
+    raws = [synth_raw_u8(i) for i in range(6)]
+    base = SynthRawBase(raws, image_size=48, normalize=True)
+    pool = MirrorExtendable(base, base.names[2:])  # rows 2..5 are the pool
+
+    class StandIn:
+        def prep(self, raw, offsets, hw, max_h, max_w, normalize):
+            assert max_h == max(r.shape[0] for r in raws) and max_w == max(r.shape[1] for r in raws)
+            imgs = []
+            for o, (h, w) in zip(offsets.tolist(), hw.tolist()):
+                imgs.append(torch.from_numpy(prep_image(raw[o:o + h * w].reshape(h, w).numpy(), (48, 48), False)))
+            x = torch.stack(imgs)
+            norm = torch.stack([x.mean((1, 2)), x.std((1, 2))], 1) if normalize else None
+            return x, norm
+
+    src = PoolSource(pool, "cpu", 4, 0, False)
+    assert src.cache is not None and src.image_hw() == (48, 48) and src.cache.n == 6
+    got = list(src.chunks([3, 0, 1], 2, StandIn()))
+    assert [g[0] for g in got] == [0, 2] and [g[1].shape[0] for g in got] == [2, 1]
+    x = torch.cat([g[1] for g in got])
+    norm = torch.cat([g[2] for g in got])
+    for k, pos in enumerate([3, 0, 1]):
+        want = pool.get_sample(pos)["image"][0]  # oracle pipeline incl. z-score
+        z = (x[k] - norm[k, 0]) / norm[k, 1]
+        assert (z - want).abs().max() < 1e-5
+    assert PoolSource(pool, "cpu", 4, 0, False).cache is src.cache          # built once per run
+    assert PoolSource(pool, "cpu", 4, 0, False, pool_cache="off").cache is None
+    base.transform = lambda d: d                                             # random transforms: never cached
+    base._b200_pool_cache = None
+    assert PoolSource(pool, "cpu", 4, 0, False).cache is None
+
+
 def test_conv_flops_match_survey():
     assert abs(b200al.conv_flops_per_sample() / 1e9 - (24.071 - 0.038 - 0.008)) < 0.02   # minus first conv and head
     assert abs(b200al.conv_flops_per_sample(encoder_only=True) / 1e9 - (8.493 - 0.038)) < 0.01

@@ -110,3 +110,46 @@ def test_reference_selector_on_mirror_datasets(ref, golden):
     scores, names = sel.cal_scores(ad, m, torch.device("cpu"))
     np.testing.assert_allclose(torch.stack(scores).numpy(), g["scores/entropy"][:n], rtol=1e-5)
     assert names == ad.get_pool_dataset().image_idx
+
+
+def test_antialiased_resize_matches_torch_and_torchvision(ref):
+    """The third-party algorithm behind JointResize (joint_transform.py:24): torch interpolate(antialias=True)."""
+    import torch.nn.functional as TF
+    import torchvision.transforms.functional as VF
+    from oracle.prep_ref import resize_bilinear_aa
+    rng = np.random.default_rng(3)
+    for hs, ws in [(336, 544), (512, 512), (256, 256), (100, 90), (257, 255), (1900, 2600), (256, 700), (31, 1024)]:
+        x = rng.random((hs, ws), dtype=np.float32)
+        want = TF.interpolate(torch.from_numpy(x)[None, None], size=(256, 256), mode="bilinear", align_corners=False,
+                              antialias=True)[0, 0].numpy()
+        tv = VF.resize(torch.from_numpy(x)[None], [256, 256], VF.InterpolationMode.BILINEAR)[0].numpy()
+        got = resize_bilinear_aa(x, (256, 256))
+        assert np.abs(got - want).max() < 1e-6, (hs, ws)
+        assert np.abs(got - tv).max() < 1e-6, (hs, ws)
+
+
+@pytest.mark.parametrize("normalize", [False, True])
+def test_input_pipeline_matches_reference_fugc_dataset(ref, tmp_path, normalize):
+    """PNG files -> the reference's FUGCDataset exactly as al_train builds the pool dataset -> oracle restatement;
+    and the pool cache's raw reader sees the same pixels the reference decodes."""
+    from b200al.pool_cache import DevicePoolCache, _raw_reader
+    from oracle.make_golden_prep import write_fugc_tree
+    from oracle.prep_ref import prep_image, synth_raw_u8
+    raws = [synth_raw_u8(i) for i in range(3, 8)]
+    names = [f"c{i}" for i in range(len(raws))]
+    write_fugc_tree(str(tmp_path), raws, names)
+    ds = ref.FUGCDataset(data_path=str(tmp_path), split="train", normalize=ref.ZScoreNormalize() if normalize else None,
+                         transform=None, image_channels=1, image_size=256)
+    read = _raw_reader(ds)
+    assert read is not None
+    for i in range(len(ds)):
+        smp = ds.get_sample(i)
+        k = names.index(smp["case_name"])
+        assert np.array_equal(read(i), raws[k])
+        got = prep_image(raws[k], (256, 256), normalize)
+        assert smp["image"].shape == (1, 256, 256)
+        assert np.abs(got - smp["image"][0].numpy()).max() < (5e-6 if normalize else 1e-6)
+    cache = DevicePoolCache.try_build(ds, "cpu")  # host-side bookkeeping only (no kernels on a CPU device)
+    assert cache is not None and cache.n == len(ds) and cache.normalize == normalize and cache.out_hw == (256, 256)
+    ds.transform = object()  # a dataset with (random) transforms must never be cached
+    assert DevicePoolCache.try_build(ds, "cpu") is None
