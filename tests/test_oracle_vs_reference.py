@@ -153,3 +153,38 @@ def test_input_pipeline_matches_reference_fugc_dataset(ref, tmp_path, normalize)
     assert cache is not None and cache.n == len(ds) and cache.normalize == normalize and cache.out_hw == (256, 256)
     ds.transform = object()  # a dataset with (random) transforms must never be cached
     assert DevicePoolCache.try_build(ds, "cpu") is None
+
+
+def test_hook_against_the_real_al_trainer(ref, monkeypatch):
+    """`install_into_al_trainer` on the reference's own ALTrainer / ALConfig (al_trainer.py:87,291,802-883): b200-*
+    names build the drop-in selectors from the real config object, the reference's names and its ValueError for
+    unknown names are untouched, and the selectors pass isinstance against the reference ABC."""
+    import importlib
+    import sys
+    import b200al
+    from oracle.ref_import import REFERENCE_SRC
+    sys.path.insert(0, REFERENCE_SRC)
+    try:
+        m = importlib.import_module("training.al_trainer")
+    finally:
+        sys.path.remove(REFERENCE_SRC)
+    monkeypatch.setattr(m.ALTrainer, "_setup_active_selector", m.ALTrainer._setup_active_selector)  # restored after
+    b200al.install_into_al_trainer(m.ALTrainer, reference_abc=ref.ActiveSelector)
+    cfg = m.ALConfig(active_selector_name="b200-coreset-l2", coreset_criteria="mean", batch_size=7, num_workers=0,
+                     pin_memory=False)
+    t = object.__new__(m.ALTrainer)  # no work dir / logger / model needed for selector set-up
+    t.config = cfg
+    t._setup_active_selector()
+    sel = t.active_selector
+    assert isinstance(sel, b200al.B200CoresetSelector) and isinstance(sel, ref.ActiveSelector)
+    assert (sel.batch_size, sel.num_workers, sel.pin_memory, sel.metric, sel.coreset_criteria) == (7, 0, False, "l2", "mean")
+    for name in b200al.SELECTORS:
+        cfg.active_selector_name = name
+        t._setup_active_selector()
+        assert isinstance(t.active_selector, ref.ActiveSelector)
+    cfg.active_selector_name = "entropy"
+    t._setup_active_selector()
+    assert type(t.active_selector) is ref.EntropySelector
+    cfg.active_selector_name = "no-such-selector"
+    with pytest.raises(ValueError):
+        t._setup_active_selector()

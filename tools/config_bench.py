@@ -3,7 +3,10 @@ GPU under torchrun): config 1 (entropy, BUSI shape, 512-image pool, budget 32), 
 100k pool, 500 labeled, budget 500), config 4 (hybrid entropy -> k-center, 100k pool, budget 500).
 Pools are synthetic (256 seeded base images tiled with circular shifts), resident in HBM as uint8.
 
-    python tools/config_bench.py [--pool 100000] [--configs 1,3,4]
+Config "p": the input pipeline alone and through a selector - a pool of ragged FUGC-/BUSI-sized raw uint8 images
+resident in HBM (device pool cache), resize + z-score statistics on the GPU per 128-image chunk.
+
+    python tools/config_bench.py [--pool 100000] [--configs 1,3,4,p]
 """
 import argparse
 import json
@@ -18,7 +21,8 @@ import numpy as np
 import torch
 
 import b200al
-from oracle.synth import MirrorActive, MirrorExtendable, SynthBase, case_name, synth_pool_u8
+from oracle.prep_ref import synth_raw_u8
+from oracle.synth import MirrorActive, MirrorExtendable, SynthBase, SynthRawBase, case_name, synth_pool_u8
 from oracle.unet_ref import OracleUNet, golden_state_dict
 
 
@@ -82,6 +86,33 @@ def main():
             dt, names = timed(lambda: sel.select_next_batch(ad, 500, model, dev), reps=1)
             out.append({"config": 4, "what": f"hybrid entropy top-5000 -> k-center, K=3, {args.pool}-image pool, budget 500",
                         "seconds": dt, "images_per_s": args.pool / dt, "selected": len(set(names))})
+        elif c == "p":
+            model = OracleUNet(golden_state_dict(3, g))
+            n = min(args.pool, 10_000)
+            distinct = [synth_raw_u8(i) for i in range(64)]
+            raws = [distinct[i % 64] for i in range(n + 32)]
+            base = SynthRawBase(raws, 256, normalize=True)
+            ad = MirrorActive(MirrorExtendable(base, base.names[:32]), MirrorExtendable(base, base.names[32:]))
+            sel = b200al.B200EntropySelector(**kw)
+            dt, names = timed(lambda: sel.select_next_batch(ad, 32, model, dev))
+            cache = base._b200_pool_cache
+            eng = b200al.selectors.get_engine(dev, 3, 256, 256, "bf16x3", 128)
+            rows = torch.arange(32, 32 + 1024, device=dev)
+            for _ in range(2):
+                cache.gather(eng, rows)
+            torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for _ in range(5):
+                cache.gather(eng, rows)
+            e1.record()
+            torch.cuda.synchronize()
+            us = e0.elapsed_time(e1) * 1e3 / (5 * 1024)
+            raw_b = sum(distinct[i % 64].size for i in range(1024)) / 1024
+            out.append({"config": "p", "what": f"entropy with --do-normalize from the ragged raw pool cache, K=3, {n}-image pool",
+                        "seconds": dt, "images_per_s": n / dt, "selected": len(names),
+                        "prep_us_per_image": us, "prep_raw_bytes_per_image": raw_b,
+                        "prep_GBps": (raw_b + 256 * 256 * 4) / us / 1e3, "cache_MB": cache.nbytes / 1e6})
     if rank == 0:
         for o in out:
             o["n_gpus"] = world
