@@ -19,6 +19,7 @@
 #ifndef B200AL_H_
 #define B200AL_H_
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -143,6 +144,19 @@ int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, int D, const
  * d_state / d_taken are updated in place. */
 int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, int criteria, int n_centres,
                        void* d_state, uint8_t* d_taken, int budget, int64_t* d_picks, float* d_pick_vals, void* stream);
+/* KMeanSelector (kmean_selector.py:19-196).
+ * standardize_rows: (x - mean) / std per row, population std (:95-97).
+ * kmeans_pp: scikit-learn's weighted k-means++ seeding (`kmeans_plusplus`, kmean_selector.py:190-192; sklearn 1.9.0
+ * `_kmeans_plusplus`) on d_X [n,D] fp32 with normalised sample weights d_weight [n] fp32.  The caller draws the random
+ * numbers from numpy's global RandomState in sklearn's order: first_centre = choice(n, p=w/w.sum()), then
+ * d_uniform [(n_clusters-1) * n_local_trials] doubles = uniform(size=n_local_trials) per further centre
+ * (n_local_trials = 2 + int(log(n_clusters)), at most 16).  d_scratch: b200al_kmeans_pp_scratch_bytes(n, trials)
+ * bytes of device memory.  d_picks [n_clusters] int64 row indices in pick order. */
+int b200al_standardize_rows(b200al_ctx* ctx, const float* d_in, float* d_out, int n, int D, void* stream);
+size_t b200al_kmeans_pp_scratch_bytes(int n, int n_local_trials);
+int b200al_kmeans_pp(b200al_ctx* ctx, const float* d_X, int n, int D, const float* d_weight, int first_centre,
+                     const double* d_uniform, int n_clusters, int n_local_trials, void* d_scratch, int64_t* d_picks,
+                     void* stream);
 int b200al_normalize_rows(b200al_ctx* ctx, const float* d_in, float* d_out, int n, int D, void* stream);
 
 /* Introspection for benches / tests. */

@@ -14,6 +14,7 @@ from .selectors import (  # noqa: F401
     B200CoresetSelector,
     B200EntropySelector,
     B200HybridSelector,
+    B200KMeanSelector,
     B200MarginSelector,
     B200MCDropoutEntropySelector,
     PoolSource,

@@ -319,6 +319,58 @@ class Engine:
                                                     self._ptr(taken), budget, self._ptr(picks), self._ptr(vals), st))
         return (picks, vals) if return_vals else picks
 
+    def centre_distances(self, feats: torch.Tensor, centres: torch.Tensor, metric: str = "l2",
+                         criteria: str = "min") -> torch.Tensor:
+        """Per row of `feats` [n,D]: min (or mean) over the rows of `centres` [L,D] of the sklearn-fp32 distance -
+        `pairwise_distances(feats, centres, metric).min(axis=1)` / `.mean(axis=1)` (kmean_selector.py:143-145,
+        175-178) without the n x L matrix.  fp32 [n] on device."""
+        feats = feats.to(device=self.device, dtype=torch.float32).contiguous()
+        centres = centres.to(device=self.device, dtype=torch.float32).contiguous()
+        n, D = feats.shape
+        L = centres.shape[0]
+        if criteria not in _lib.CRITERIA:
+            raise RuntimeError(f"coreset_criteria {criteria} is undefined")
+        st = self._stream()
+        with torch.cuda.device(self.device):
+            if metric == "cosine":
+                fn, cn = torch.empty_like(feats), torch.empty_like(centres)
+                self._check(self.lib.b200al_normalize_rows(self.ctx, self._ptr(feats), self._ptr(fn), n, D, st))
+                self._check(self.lib.b200al_normalize_rows(self.ctx, self._ptr(centres), self._ptr(cn), L, D, st))
+                feats, centres = fn, cn
+            state = torch.empty(n, dtype=torch.float64 if criteria == "mean" else torch.float32, device=self.device)
+            self._check(self.lib.b200al_kcenter_init(self.ctx, self._ptr(feats), n, D, self._ptr(centres), L,
+                                                     _lib.METRICS[metric], _lib.CRITERIA[criteria], self._ptr(state),
+                                                     0, st))
+        return (state / L).to(torch.float32) if criteria == "mean" else state
+
+    def standardize_rows(self, feats: torch.Tensor) -> torch.Tensor:
+        """(x - mean) / std per row, population std (kmean_selector.py:95-97)."""
+        feats = feats.to(device=self.device, dtype=torch.float32).contiguous()
+        out = torch.empty_like(feats)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.b200al_standardize_rows(self.ctx, self._ptr(feats), self._ptr(out), feats.shape[0],
+                                                         feats.shape[1], self._stream()))
+        return out
+
+    def kmeans_pp(self, X: torch.Tensor, weights: torch.Tensor, first_centre: int, uniforms: torch.Tensor,
+                  n_clusters: int, n_local_trials: int) -> torch.Tensor:
+        """scikit-learn's weighted k-means++ seeding on rows of X [n,D] (fp32, device) with the host-drawn random
+        numbers (`first_centre`, `uniforms` [(n_clusters-1), n_local_trials] float64).  Row indices, pick order."""
+        X = X.to(device=self.device, dtype=torch.float32).contiguous()
+        n, D = X.shape
+        weights = weights.to(device=self.device, dtype=torch.float32).contiguous()
+        uniforms = uniforms.to(device=self.device, dtype=torch.float64).contiguous()
+        if weights.shape != (n,) or uniforms.numel() != max(0, n_clusters - 1) * n_local_trials:
+            raise ValueError("weights must be [n] and uniforms [(n_clusters-1) * n_local_trials]")
+        picks = torch.empty(n_clusters, dtype=torch.int64, device=self.device)
+        nbytes = self.lib.b200al_kmeans_pp_scratch_bytes(n, n_local_trials)
+        scratch = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        with torch.cuda.device(self.device):
+            self._check(self.lib.b200al_kmeans_pp(self.ctx, self._ptr(X), n, D, self._ptr(weights), int(first_centre),
+                                                  self._ptr(uniforms), int(n_clusters), int(n_local_trials),
+                                                  self._ptr(scratch), self._ptr(picks), self._stream()))
+        return picks
+
     # ---------------------------------------------------------- introspection
     def kernel_launches(self) -> int:
         c = C.c_int64()

@@ -27,6 +27,10 @@ def install_into_al_trainer(trainer_cls, reference_abc=None):
             if name.startswith("b200-coreset"):  # al_trainer.py:823-844 forwards these two to CoresetSelector
                 kw["coreset_criteria"] = getattr(self.config, "coreset_criteria", "min")
                 kw["coreset_fusion"] = getattr(self.config, "coreset_fusion", "add")
+            if name.startswith("b200-kmean"):  # al_trainer.py:845-870
+                kw["coreset_criteria"] = getattr(self.config, "coreset_criteria", "min")
+                kw["sharp_factor"] = getattr(self.config, "kmean_sharp_factor", 1.0)
+                kw["softmax"] = getattr(self.config, "kmean_softmax", False)
             self.active_selector = SELECTORS[name](**kw)
         else:
             original(self)

@@ -318,6 +318,77 @@ class B200CoresetSelector(_B200Base):
         return [all_list[i] for i in picks.tolist()]
 
 
+class B200KMeanSelector(_B200Base):
+    """KMeanSelector (src/activelearning/kmean_selector.py:19-196), model features only: row-standardised
+    `get_enc_feature` embeddings (:95-97), sample weight = min / mean distance of each pool row to the labeled rows
+    (:143-145, 174-186) and scikit-learn's weighted k-means++ seeding over the pool (:190-192).
+
+    The random numbers come from numpy's GLOBAL RandomState in sklearn's call order (one `choice`, then
+    `uniform(size=2+int(log k))` per further centre), so a seeded run consumes the same stream as the reference.
+    Embedding, standardisation, pool-to-labeled distances and the whole seeding loop run on the GPU; the O(n)
+    weight normalisation and the draws stay on the host in the reference's own numpy / torch calls.  Names are
+    returned in pick order, duplicates dropped (the reference returns `list(set(...))`, :194).  Without labeled data
+    the weights are uniform (:187-188) - this selector has no random cold-start branch."""
+
+    def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8,
+                 metric: str = "cosine", feature_path=None, feature_dict=None, coreset_criteria: str = "min",
+                 loaded_feature_weight: float = 1.0, loaded_feature_only: bool = False, sharp_factor: float = 1.0,
+                 softmax: bool = False, **kw):
+        super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
+        if metric not in ("l2", "cosine"):
+            raise NotImplementedError(f"metric {metric!r}: only 'l2' and 'cosine' are supported")
+        if coreset_criteria not in ("min", "mean"):
+            raise RuntimeError(f"coreset_criteria {coreset_criteria} is undefined")
+        if feature_path is not None or feature_dict is not None or loaded_feature_only:
+            raise NotImplementedError("externally loaded features (feature_path / feature_dict / loaded_feature_only) "
+                                      "are not supported")
+        self.metric, self.coreset_criteria = metric, coreset_criteria
+        self.sharp_factor, self.softmax = sharp_factor, bool(softmax)
+        self.loaded_feature_weight = loaded_feature_weight
+
+    def select_next_batch(self, active_dataset, select_num: int, model, device):
+        import numpy as np
+        labeled_size, pool_size = active_dataset.get_size()
+        if select_num <= 0:
+            return []
+        if pool_size < select_num:  # sklearn's own check inside kmeans_plusplus
+            raise ValueError(f"n_samples={pool_size} should be >= n_clusters={select_num}.")
+        labeled, pool = active_dataset.get_train_dataset(), active_dataset.get_pool_dataset()
+        rank, ws = D.world()
+        lo, hi = D.shard_range(pool_size, rank, ws)
+        psrc = self._source(pool, device)
+        eng = self._engine(model, device, psrc.image_hw())
+        X = eng.standardize_rows(D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi)))))
+        if labeled_size > 0:
+            lsrc = self._source(labeled, device)
+            Xl = eng.standardize_rows(_embed_positions(eng, lsrc, list(range(labeled_size))))
+            w = eng.centre_distances(X, Xl, self.metric, self.coreset_criteria).cpu()
+            if self.softmax:  # kmean_selector.py:180-183
+                w = (w * self.sharp_factor).softmax(0).numpy()
+            else:             # :184-186
+                w = w.numpy() ** self.sharp_factor
+                w = w / w.sum()
+        else:
+            w = np.ones(pool_size, dtype=np.float32)  # sklearn _check_sample_weight(None)
+        w = np.asarray(w, dtype=np.float32)
+        rs = np.random.mtrand._rand  # check_random_state(None): numpy's global RandomState
+        trials = 2 + int(np.log(select_num))
+        first = int(rs.choice(pool_size, p=w / w.sum()))
+        uniforms = np.stack([rs.uniform(size=trials) for _ in range(select_num - 1)]) if select_num > 1 \
+            else np.zeros((0, trials))
+        if ws > 1:  # every rank consumed its own stream; rank 0's draws decide so that all ranks agree
+            t = torch.from_numpy(np.concatenate([[float(first)], uniforms.reshape(-1)])).to(eng.device)
+            torch.distributed.broadcast(t, src=0)
+            first, uniforms = int(t[0].item()), t[1:].cpu().numpy().reshape(-1, trials)
+        picks = eng.kmeans_pp(X, torch.from_numpy(w), first, torch.from_numpy(uniforms), select_num, trials).tolist()
+        seen, out = set(), []
+        for i in picks:
+            if i not in seen:
+                seen.add(i)
+                out.append(pool.image_idx[i])
+        return out
+
+
 class B200HybridSelector(_B200Uncertainty):
     """Uncertainty pre-filter (top `prefilter_factor * select_num` by score)
     followed by k-center greedy (l2) on the survivors' embeddings.  Not in the
@@ -360,4 +431,6 @@ SELECTORS = {
     "b200-coreset-l2": lambda **kw: B200CoresetSelector(metric="l2", **kw),
     "b200-coreset-cosine": lambda **kw: B200CoresetSelector(metric="cosine", **kw),
     "b200-hybrid": B200HybridSelector,
+    "b200-kmean-l2": lambda **kw: B200KMeanSelector(metric="l2", **kw),
+    "b200-kmean-cosine": lambda **kw: B200KMeanSelector(metric="cosine", **kw),
 }

@@ -17,6 +17,7 @@
 #include "conv_fold.cuh"
 #include "conv_tc.cuh"
 #include "kcenter.cuh"
+#include "kmeanpp.cuh"
 #include "prep.cuh"
 #include "topk.cuh"
 #include "uncertainty.cuh"
@@ -1040,6 +1041,85 @@ extern "C" int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, i
     case 8: launch_kc_init<8>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
   }
   ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+extern "C" int b200al_standardize_rows(b200al_ctx* ctx, const float* d_in, float* d_out, int n, int D, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (n == 0) return B200AL_OK;
+  if (!d_in || !d_out || n < 0 || D < 2) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  standardize_rows_kernel<<<(n + 7) / 8, 256, 0, st>>>(d_in, d_out, n, D);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+extern "C" size_t b200al_kmeans_pp_scratch_bytes(int n, int n_local_trials) {
+  if (n < 1 || n_local_trials < 1) return 0;
+  const size_t blocks = 148 * 8;
+  return ((size_t)n * (n_local_trials + 1)) * sizeof(float) + blocks * n_local_trials * sizeof(double) + 256;
+}
+
+namespace {
+template <int NV>
+void launch_kmpp_dist(const float* X, const float* w, int n, const int* cand, int trials, const float* closest, int first,
+                      float* cand_d, double* part, int blocks, cudaStream_t st) {
+  const size_t smem = (size_t)trials * NV * 128 * sizeof(float);
+  cudaFuncSetAttribute(kmpp_dist_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  kmpp_dist_kernel<NV><<<blocks, 256, smem, st>>>(X, w, n, cand, trials, closest, first, cand_d, part);
+}
+}  // namespace
+
+extern "C" int b200al_kmeans_pp(b200al_ctx* ctx, const float* d_X, int n, int D, const float* d_weight, int first_centre,
+                                const double* d_uniform, int n_clusters, int n_local_trials, void* d_scratch,
+                                int64_t* d_picks, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (n_clusters == 0) return B200AL_OK;
+  if (!d_X || !d_weight || !d_scratch || !d_picks || n < 1 || n_clusters < 0 || first_centre < 0 || first_centre >= n)
+    return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (n_clusters > n) return set_err(ctx, B200AL_ERR_ARG, "n_samples=%d should be >= n_clusters=%d", n, n_clusters);
+  if (n_local_trials < 1 || n_local_trials > kKmppMaxTrials)
+    return set_err(ctx, B200AL_ERR_ARG, "n_local_trials must be in [1, %d]", kKmppMaxTrials);
+  if (n_clusters > 1 && !d_uniform) return set_err(ctx, B200AL_ERR_ARG, "d_uniform is NULL");
+  if (int rc = check_dim(ctx, D)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int blocks = (n + 63) / 64;
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  const int trials = n_local_trials;
+  // scratch: closest [n] | cand_d [trials][n] | part [trials][blocks] doubles | pot, best, cand[16]
+  float* closest = (float*)d_scratch;
+  float* cand_d = closest + n;
+  size_t off = ((size_t)n * (trials + 1) * sizeof(float) + 15) & ~(size_t)15;
+  double* part = (double*)((char*)d_scratch + off);
+  off += (size_t)148 * 8 * trials * sizeof(double);
+  float* pot = (float*)((char*)d_scratch + off);
+  int* best = (int*)(pot + 1);
+  int* cand = best + 1;
+  long long* picks = (long long*)d_picks;
+#define KMPP_DIST(TR, FIRST)                                                                                   \
+  switch (D / 128) {                                                                                           \
+    case 1: launch_kmpp_dist<1>(d_X, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 2: launch_kmpp_dist<2>(d_X, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 4: launch_kmpp_dist<4>(d_X, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 8: launch_kmpp_dist<8>(d_X, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+  }
+  kmpp_set_first_kernel<<<1, 1, 0, st>>>(cand, first_centre);
+  KMPP_DIST(1, 1)
+  kmpp_pick_kernel<<<1, 32, 0, st>>>(part, blocks, cand, 1, pot, best, picks);
+  kmpp_commit_kernel<<<blocks, 256, 0, st>>>(cand_d, best, n, closest);
+  ctx->launches += 4;
+  for (int c = 1; c < n_clusters; ++c) {
+    kmpp_sample_kernel<<<1, 1024, 0, st>>>(d_weight, closest, n, d_uniform + (size_t)(c - 1) * trials, trials, pot, cand);
+    KMPP_DIST(trials, 0)
+    kmpp_pick_kernel<<<1, 32, 0, st>>>(part, blocks, cand, trials, pot, best, picks + c);
+    kmpp_commit_kernel<<<blocks, 256, 0, st>>>(cand_d, best, n, closest);
+    ctx->launches += 4;
+  }
+#undef KMPP_DIST
   CUDA_TRY(ctx, cudaGetLastError());
   return B200AL_OK;
 }

@@ -101,6 +101,7 @@ def load_reference() -> SimpleNamespace:
         MarginSelector=al.MarginSelector,
         ConfidenceSelector=al.ConfidenceSelector,
         CoresetSelector=al.CoresetSelector,
+        KMeanSelector=al.KMeanSelector,
         kcenter_greedy=cs.kcenter_greedy,
         UNet=unet_mod.UNet,
         ActiveDataset=ds.ActiveDataset,

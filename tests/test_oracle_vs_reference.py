@@ -188,3 +188,25 @@ def test_hook_against_the_real_al_trainer(ref, monkeypatch):
     cfg.active_selector_name = "no-such-selector"
     with pytest.raises(ValueError):
         t._setup_active_selector()
+
+
+def test_kmean_oracle_matches_reference_selector_live(ref, golden):
+    """Live run of the reference KMeanSelector (not the frozen golden): fresh seed, K=3 pool."""
+    from oracle import select_ref as S
+    from oracle.kmean_ref import kmean_select
+    from oracle.ref_import import build_reference_unet
+    from oracle.synth import case_name, make_active, synth_pool_u8
+    from oracle.unet_ref import golden_state_dict
+    sd = golden_state_dict(3, golden["model"])
+    model = build_reference_unet(3)
+    model.load_state_dict(sd)
+    images = synth_pool_u8(10 + 40, start=300)
+    emb = S.pool_embeddings(sd, images)
+    for kw in (dict(metric="cosine"), dict(metric="l2", coreset_criteria="mean", sharp_factor=2.0)):
+        sel = ref.KMeanSelector(batch_size=8, num_workers=0, pin_memory=False, **kw)
+        np.random.seed(99)
+        want = sel.select_next_batch(make_active(images, 10, reference=ref), 7, model, torch.device("cpu"))
+        idx = kmean_select(emb[10:], emb[:10], 7, kw["metric"], kw.get("coreset_criteria", "min"),
+                           kw.get("sharp_factor", 1.0), False, np.random.RandomState(99))
+        names = make_active(images, 10).get_pool_dataset().image_idx
+        assert sorted(want) == sorted({names[int(i)] for i in idx})
