@@ -118,6 +118,15 @@ int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int image_dtype, c
 int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, const float* d_norm, int n,
                       float* d_emb_out, void* stream);
 
+/* BADGESelector.cal_scores (badge_selector.py:56-104): per image the gradient of
+ * CrossEntropyLoss(logits, preds) + DiceLoss(logits, preds) w.r.t. decoder.seg_output.weight, preds = argmax softmax
+ * (:79-80, 91-95), in closed form over the last feature map instead of an autograd backward (csrc/badge.cuh).
+ * dice_smooth / dice_do_bg: DiceLoss(smooth, do_bg) as the trainer configures it (al_trainer.py:785-791: 1e-5, True;
+ * softmax=True, batch=False, squared=False are assumed).  d_emb_out [n][out_stride] fp32: K*32 entries in
+ * `weight.grad.flatten()` order, zero-padded to out_stride (use 128 to feed b200al_kmeans_pp).  K <= 4. */
+int b200al_badge_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, const float* d_norm, int n,
+                       float dice_smooth, int dice_do_bg, float* d_emb_out, int out_stride, void* stream);
+
 /* Kernel 3 alone: scores from fp32 logits [n,T,K,HW] already in HBM
  * (softmax -> mean over T -> entropy / margin / confidence -> mean over pixels). */
 int b200al_uncertainty_from_logits(b200al_ctx* ctx, const float* d_logits, int n, int T, int K, int HW, int mode,

@@ -10,6 +10,7 @@ from .engine import Engine, conv_flops_per_sample, validate_state_dict  # noqa: 
 from .selectors import (  # noqa: F401
     SELECTORS,
     ActiveSelector,
+    B200BADGESelector,
     B200ConfidenceSelector,
     B200CoresetSelector,
     B200EntropySelector,

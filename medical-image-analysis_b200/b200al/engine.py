@@ -255,6 +255,26 @@ class Engine:
                                                        self._ptr(out[i:i + m]), st))
         return out
 
+    def badge_embed(self, images: torch.Tensor, norm: torch.Tensor | None = None, dice_smooth: float = 1e-5,
+                    dice_do_bg: bool = True, pad_to: int = 128) -> torch.Tensor:
+        """BADGE gradient embeddings (badge_selector.py:56-104): [n, pad_to] fp32 on device, the first K*32 columns
+        are `decoder.seg_output.weight.grad.flatten()` of CE + Dice against the model's own pseudo-labels, the rest 0."""
+        imgs, dt = self._images(images)
+        n = imgs.shape[0]
+        norm = self._norm(norm, n)
+        if pad_to < self.K * 32:
+            raise ValueError(f"pad_to must be >= K*32 = {self.K * 32}")
+        out = torch.empty((n, pad_to), dtype=torch.float32, device=self.device)
+        st = self._stream()
+        with torch.cuda.device(self.device):
+            for i in range(0, n, self.max_samples):
+                m = min(self.max_samples, n - i)
+                self._check(self.lib.b200al_badge_embed(self.ctx, self._ptr(imgs[i:i + m]), dt,
+                                                        self._ptr(norm[i:i + m] if norm is not None else None), m,
+                                                        float(dice_smooth), int(bool(dice_do_bg)),
+                                                        self._ptr(out[i:i + m]), pad_to, st))
+        return out
+
     def uncertainty_from_logits(self, logits: torch.Tensor, mode: str = "entropy", smooth: float = 1e-8):
         """logits [n,K,H,W] or [n,T,K,H,W] fp32 on device -> scores [n]."""
         if logits.dim() == 4:

@@ -389,6 +389,82 @@ class B200KMeanSelector(_B200Base):
         return out
 
 
+def _dice_params(dice_loss) -> tuple[float, bool]:
+    """(smooth, do_bg) of the trainer's DiceLoss instance (src/losses/dice_loss.py:7-30); anything the closed form in
+    csrc/badge.cuh does not cover is rejected."""
+    if dice_loss is None:
+        return 1e-5, True  # al_trainer.py:785-791
+    if not getattr(dice_loss, "softmax", True) or getattr(dice_loss, "squared", False):
+        raise NotImplementedError("BADGE: only DiceLoss(softmax=True, squared=False) is supported")
+    return float(getattr(dice_loss, "smooth", 1e-5)), bool(getattr(dice_loss, "do_bg", True))
+
+
+def _check_ce(ce_loss) -> None:
+    if ce_loss is None:
+        return
+    import torch.nn as nn
+    if not isinstance(ce_loss, nn.CrossEntropyLoss) or ce_loss.weight is not None or ce_loss.reduction != "mean" \
+            or getattr(ce_loss, "label_smoothing", 0.0) != 0.0:
+        raise NotImplementedError("BADGE: only a plain torch.nn.CrossEntropyLoss() (mean reduction, no class weights, "
+                                  "no label smoothing) is supported")
+
+
+class B200BADGESelector(_B200Base):
+    """BADGESelector (src/activelearning/badge_selector.py:37-128): per-image gradient embedding of
+    `decoder.seg_output.weight` under CE + Dice against the model's own pseudo-labels, then scikit-learn's
+    (unweighted) k-means++ seeding over the pool with numpy's global RNG.  The reference runs one autograd backward
+    per image (batch_size is forced to 1, al_trainer.py:875); here the head-weight gradient is evaluated in closed
+    form from the last feature map in two fused passes (csrc/badge.cuh), chunked like the other selectors.
+    `dice_loss` / `ce_loss`: the trainer's loss modules (al_trainer.py:872-874) - only their hyper-parameters are read.
+    """
+
+    def __init__(self, dice_loss=None, ce_loss=None, batch_size: int = 1, num_workers: int = 0, pin_memory: bool = True,
+                 smooth: float = 1e-8, multiple_loss: str = "add", **kw):
+        super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
+        if multiple_loss != "add":  # "sep" concatenates two 0-d loss tensors in the reference (:90) and cannot run
+            raise NotImplementedError("multiple_loss='sep' is broken in the reference (badge_selector.py:90); use 'add'")
+        self.dice_smooth, self.dice_do_bg = _dice_params(dice_loss)
+        _check_ce(ce_loss)
+        self.multiple_loss = multiple_loss
+
+    def cal_scores(self, active_dataset, model, device):
+        """(case names, gradient embeddings [n, K*32] on device) of the whole pool, like badge_selector.py:56-104."""
+        pool = active_dataset.get_pool_dataset()
+        rank, ws = D.world()
+        lo, hi = D.shard_range(len(pool), rank, ws)
+        src = self._source(pool, device)
+        eng = self._engine(model, device, src.image_hw())
+        out = torch.empty((hi - lo, 128), dtype=torch.float32, device=eng.device)
+        for off, imgs, norm in src.chunks(list(range(lo, hi)), eng.max_samples, eng):
+            out[off:off + imgs.shape[0]] = eng.badge_embed(imgs, norm, self.dice_smooth, self.dice_do_bg, 128)
+        return list(pool.image_idx), D.gather_rows(out)[:, :eng.K * 32], eng
+
+    def select_next_batch(self, active_dataset, select_num: int, model, device):
+        import numpy as np
+        labeled_size, pool_size = active_dataset.get_size()
+        if labeled_size == 0:
+            return _cold_start(active_dataset, select_num)  # badge_selector.py:114-121
+        if select_num <= 0:
+            return []
+        if pool_size < select_num:
+            raise ValueError(f"n_samples={pool_size} should be >= n_clusters={select_num}.")
+        names, emb, eng = self.cal_scores(active_dataset, model, device)
+        X = torch.zeros((pool_size, 128), dtype=torch.float32, device=eng.device)
+        X[:, :emb.shape[1]] = emb  # zero columns do not change any distance
+        rs = np.random.mtrand._rand
+        trials = 2 + int(np.log(select_num))
+        w = np.ones(pool_size, dtype=np.float32)  # sample_weight=None
+        first = int(rs.choice(pool_size, p=w / w.sum()))
+        uniforms = np.stack([rs.uniform(size=trials) for _ in range(select_num - 1)]) if select_num > 1 \
+            else np.zeros((0, trials))
+        if D.world()[1] > 1:
+            t = torch.from_numpy(np.concatenate([[float(first)], uniforms.reshape(-1)])).to(eng.device)
+            torch.distributed.broadcast(t, src=0)
+            first, uniforms = int(t[0].item()), t[1:].cpu().numpy().reshape(-1, trials)
+        picks = eng.kmeans_pp(X, torch.from_numpy(w), first, torch.from_numpy(uniforms), select_num, trials).tolist()
+        return [names[i] for i in picks]  # pick order, like list(case_name_list[selected_indices]) (:126)
+
+
 class B200HybridSelector(_B200Uncertainty):
     """Uncertainty pre-filter (top `prefilter_factor * select_num` by score)
     followed by k-center greedy (l2) on the survivors' embeddings.  Not in the
@@ -433,4 +509,5 @@ SELECTORS = {
     "b200-hybrid": B200HybridSelector,
     "b200-kmean-l2": lambda **kw: B200KMeanSelector(metric="l2", **kw),
     "b200-kmean-cosine": lambda **kw: B200KMeanSelector(metric="cosine", **kw),
+    "b200-badge": B200BADGESelector,
 }

@@ -13,6 +13,7 @@
 #include <string>
 #include <vector>
 
+#include "badge.cuh"
 #include "common.cuh"
 #include "conv_fold.cuh"
 #include "conv_tc.cuh"
@@ -93,6 +94,9 @@ struct b200al_ctx {
   bool fuse_head = false;
   double* partial = nullptr;
   int partial_blocks = 0;
+  double* badge_stats = nullptr;  // [max_samples][kBadgeBlocks][3K]
+  double* badge_grad = nullptr;   // [max_samples][kBadgeBlocks][K*32]
+  float* badge_coef = nullptr;    // [max_samples][2K]
   double* prep_partials = nullptr;  // [max_samples][ceil(H / kPrepBand)][2] z-score partial sums
   float slope = 0.01f;
   // k-center / top-k scratch
@@ -919,6 +923,54 @@ extern "C" int b200al_unet_embed(b200al_ctx* ctx, const void* d_images, int imag
   avgpool_kernel<<<n, 512, 0, st>>>(bb.ptr, (ctx->H >> 4) * (ctx->W >> 4), 2 * bb.c_total, 0, bb.c_total,
                                     ctx->nsplit == 3, bb.c_total, d_emb_out);
   ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+namespace {
+template <int K>
+void launch_badge(b200al_ctx* ctx, int n, float smooth, int do_bg, float* out, int out_stride, cudaStream_t st) {
+  const ActBuf& fb = ctx->bufs[D3B];
+  const int HW = ctx->H * ctx->W;
+  dim3 grid(kBadgeBlocks, n);
+  badge_stats_kernel<K><<<grid, 256, 0, st>>>(fb.ptr, 2 * fb.c_total, 0, fb.c_total, ctx->nsplit == 3, HW, ctx->head_w,
+                                             ctx->head_b, ctx->badge_stats);
+  badge_coef_kernel<K><<<(n + 127) / 128, 128, 0, st>>>(ctx->badge_stats, kBadgeBlocks, smooth, do_bg, ctx->badge_coef, n);
+  badge_grad_kernel<K><<<grid, 256, 0, st>>>(fb.ptr, 2 * fb.c_total, 0, fb.c_total, ctx->nsplit == 3, HW, ctx->head_w,
+                                            ctx->head_b, ctx->badge_coef, ctx->badge_grad);
+  badge_reduce_kernel<<<(n * out_stride + 255) / 256, 256, 0, st>>>(ctx->badge_grad, kBadgeBlocks, K * 32, out_stride,
+                                                                   out, n);
+}
+}  // namespace
+
+extern "C" int b200al_badge_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, const float* d_norm, int n,
+                                  float dice_smooth, int dice_do_bg, float* d_emb_out, int out_stride, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (!ctx->weights_loaded) return set_err(ctx, B200AL_ERR_STATE, "b200al_load_weights has not been called");
+  if (n == 0) return B200AL_OK;
+  if (!d_images || !d_emb_out || n < 0) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (n > ctx->max_samples) return set_err(ctx, B200AL_ERR_ARG, "n = %d exceeds max_samples = %d", n, ctx->max_samples);
+  if (ctx->K > kBadgeMaxK) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "BADGE embedding supports up to %d classes", kBadgeMaxK);
+  if (out_stride < ctx->K * 32) return set_err(ctx, B200AL_ERR_ARG, "out_stride must be >= K*32 = %d", ctx->K * 32);
+  if (!dice_do_bg && ctx->K < 2) return set_err(ctx, B200AL_ERR_ARG, "do_bg = 0 needs K >= 2");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int rc;
+  if (!ctx->badge_stats) {  // scratch of the BADGE path, allocated on first use, freed with the context
+    if ((rc = dev_alloc(ctx, &ctx->badge_stats, (size_t)ctx->max_samples * kBadgeBlocks * 3 * kBadgeMaxK))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->badge_grad, (size_t)ctx->max_samples * kBadgeBlocks * 32 * kBadgeMaxK))) return rc;
+    if ((rc = dev_alloc(ctx, &ctx->badge_coef, (size_t)ctx->max_samples * 2 * kBadgeMaxK))) return rc;
+  }
+  if ((rc = run_first_conv(ctx, d_images, image_dtype, d_norm, n, 1, nullptr, st))) return rc;
+  // all 21 conv layers WITHOUT the fused head: the last block leaves its 32-channel feature map in HBM
+  if ((rc = run_layers(ctx, (int)ctx->layers.size(), n, nullptr, st))) return rc;
+  switch (ctx->K) {
+    case 2: launch_badge<2>(ctx, n, dice_smooth, dice_do_bg, d_emb_out, out_stride, st); break;
+    case 3: launch_badge<3>(ctx, n, dice_smooth, dice_do_bg, d_emb_out, out_stride, st); break;
+    case 4: launch_badge<4>(ctx, n, dice_smooth, dice_do_bg, d_emb_out, out_stride, st); break;
+    default: break;
+  }
+  ctx->launches += 4;
   CUDA_TRY(ctx, cudaGetLastError());
   return B200AL_OK;
 }

@@ -1,0 +1,90 @@
+"""BADGESelector on the GPU: the head-weight gradient embedding in closed form over the last
+feature map (csrc/badge.cuh) vs the reference's autograd embeddings frozen in tests/golden/badge.npz, and the drop-in
+selector's picks (k-means++ over those embeddings, numpy global RNG) vs the reference BADGESelector's."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _golden():
+    return np.load(os.path.join(os.path.dirname(__file__), "golden", "badge.npz"))
+
+
+@pytest.mark.parametrize("key,K,n_lab,do_bg", [("K3", 3, 8, True), ("K2", 2, 8, True), ("K3/nobg", 3, 8, False)])
+def test_gradient_embeddings_match_reference(golden, key, K, n_lab, do_bg):
+    import b200al
+    from oracle.synth import synth_pool_u8
+    from oracle.unet_ref import golden_state_dict
+    want = _golden()["emb/" + key]
+    imgs = synth_pool_u8(want.shape[0], start=n_lab).to(DEV)
+    eng = b200al.Engine(DEV, K, max_samples=16)  # 24 images > max_samples: chunked
+    try:
+        eng.load_model(golden_state_dict(K, golden["model"]))
+        got = eng.badge_embed(imgs, dice_do_bg=do_bg)
+        assert got.shape == (want.shape[0], 128)
+        assert torch.count_nonzero(got[:, K * 32:]).item() == 0
+        got = got[:, :K * 32].cpu().numpy()
+        # Pseudo-labels are an argmax: logits within the north star's 2e-2 tolerance (here ~3e-4) flip the label of
+        # the few pixels whose top two classes tie that closely, each moving the gradient by ~|feat| / (H*W).  Bound:
+        # 3e-3 of the embedding's own scale per image, 2e-4 in the mean.
+        scale = np.abs(want).max(axis=1, keepdims=True)
+        err = np.abs(got - want) / scale
+        assert err.max() < 3e-3 and err.mean() < 2e-4, (err.max(), err.mean())
+        # z-scored inputs go through the same path (norm applied by the first conv's loader)
+        f = imgs[:4].float().div(255)
+        norm = torch.stack([f.mean((1, 2)), f.std((1, 2))], 1)
+        z = (f - norm[:, 0, None, None]) / norm[:, 1, None, None]
+        a, b = eng.badge_embed(f, norm=norm, dice_do_bg=do_bg), eng.badge_embed(z, dice_do_bg=do_bg)
+        assert (a - b).abs().max().item() <= 1e-4 * b.abs().max().item()
+    finally:
+        eng.close()
+
+
+@pytest.mark.parametrize("key,K,n_lab", [("K3", 3, 8), ("K2", 2, 8)])
+def test_badge_selector_picks_reference_names_in_order(golden, key, K, n_lab):
+    import b200al
+    from oracle.synth import make_active, synth_pool_u8
+    from oracle.unet_ref import OracleUNet, golden_state_dict
+    gb = _golden()
+    want = gb["selected/" + key].tolist()
+    model = OracleUNet(golden_state_dict(K, golden["model"]))
+    ad = make_active(synth_pool_u8(n_lab + gb["emb/" + key].shape[0]), n_lab)
+    sel = b200al.B200BADGESelector(batch_size=1, num_workers=0, pin_memory=False)
+    np.random.seed(int(gb["seed/" + key]))
+    got = sel.select_next_batch(ad, len(want), model, torch.device(DEV))
+    assert got == want
+    assert sel.last_timing["selected"] == len(want)
+
+
+def test_badge_selector_contract(golden):
+    import b200al
+    from oracle.synth import make_active, synth_pool_u8
+    from oracle.unet_ref import OracleUNet, golden_state_dict
+    with pytest.raises(NotImplementedError):
+        b200al.B200BADGESelector(multiple_loss="sep")
+    with pytest.raises(NotImplementedError):
+        b200al.B200BADGESelector(ce_loss=torch.nn.CrossEntropyLoss(weight=torch.ones(3)))
+
+    class Dice:  # hyper-parameters are read off the trainer's DiceLoss instance
+        smooth, do_bg, softmax, squared, batch = 1e-3, False, True, False, False
+
+    s = b200al.B200BADGESelector(dice_loss=Dice(), ce_loss=torch.nn.CrossEntropyLoss())
+    assert (s.dice_smooth, s.dice_do_bg) == (1e-3, False)
+    Dice.squared = True
+    with pytest.raises(NotImplementedError):
+        b200al.B200BADGESelector(dice_loss=Dice())
+    # cold start: the reference's seeded random branch (badge_selector.py:114-121)
+    model = OracleUNet(golden_state_dict(2, golden["model"]))
+    ad0 = make_active(synth_pool_u8(9), 0)
+    torch.manual_seed(11)
+    got = b200al.SELECTORS["b200-badge"](batch_size=1, num_workers=0).select_next_batch(ad0, 4, model, torch.device(DEV))
+    torch.manual_seed(11)
+    _, idx = torch.sort(torch.rand(9), descending=True)
+    assert got == [ad0.get_pool_dataset().image_idx[i] for i in idx[:4]]
+    with pytest.raises(ValueError):  # sklearn's n_samples < n_clusters
+        b200al.B200BADGESelector().select_next_batch(make_active(synth_pool_u8(6), 2), 5, model, torch.device(DEV))

@@ -174,6 +174,7 @@ def test_hook_against_the_real_al_trainer(ref, monkeypatch):
                      pin_memory=False)
     t = object.__new__(m.ALTrainer)  # no work dir / logger / model needed for selector set-up
     t.config = cfg
+    t._setup_loss()  # the real DiceAndCELoss (al_trainer.py:782-798): b200-badge reads its dice / ce modules
     t._setup_active_selector()
     sel = t.active_selector
     assert isinstance(sel, b200al.B200CoresetSelector) and isinstance(sel, ref.ActiveSelector)
@@ -182,6 +183,9 @@ def test_hook_against_the_real_al_trainer(ref, monkeypatch):
         cfg.active_selector_name = name
         t._setup_active_selector()
         assert isinstance(t.active_selector, ref.ActiveSelector)
+    cfg.active_selector_name = "b200-badge"
+    t._setup_active_selector()
+    assert (t.active_selector.dice_smooth, t.active_selector.dice_do_bg) == (1e-5, True)
     cfg.active_selector_name = "entropy"
     t._setup_active_selector()
     assert type(t.active_selector) is ref.EntropySelector
@@ -210,3 +214,28 @@ def test_kmean_oracle_matches_reference_selector_live(ref, golden):
                            kw.get("sharp_factor", 1.0), False, np.random.RandomState(99))
         names = make_active(images, 10).get_pool_dataset().image_idx
         assert sorted(want) == sorted({names[int(i)] for i in idx})
+
+
+def test_badge_oracle_bit_identical_to_reference_cal_scores(ref, golden):
+    import importlib
+    import sys
+    from oracle.badge_ref import grad_embedding_autograd
+    from oracle.ref_import import REFERENCE_SRC, build_reference_unet
+    from oracle.synth import make_active, synth_pool_u8
+    from oracle.unet_ref import golden_state_dict
+    sys.path.insert(0, REFERENCE_SRC)
+    try:
+        al = importlib.import_module("activelearning")
+        dl = importlib.import_module("losses.dice_loss")
+    finally:
+        sys.path.remove(REFERENCE_SRC)
+    sd = golden_state_dict(3, golden["model"])
+    model = build_reference_unet(3)
+    model.load_state_dict(sd)
+    images = synth_pool_u8(2 + 3, start=700)
+    for do_bg in (True, False):
+        dice = dl.DiceLoss(num_classes=2, smooth=1e-5, do_bg=do_bg, softmax=True, batch=False, squared=False)
+        sel = al.BADGESelector(dice_loss=dice, ce_loss=torch.nn.CrossEntropyLoss(), batch_size=1, num_workers=0,
+                               pin_memory=False)
+        _names, emb = sel.cal_scores(make_active(images, 2, reference=ref), model, torch.device("cpu"))
+        assert np.array_equal(emb, grad_embedding_autograd(sd, images[2:].float().div(255).unsqueeze(1), 1e-5, do_bg))
