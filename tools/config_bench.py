@@ -6,7 +6,7 @@ Pools are synthetic (256 seeded base images tiled with circular shifts), residen
 Config "p": the input pipeline alone and through a selector - a pool of ragged FUGC-/BUSI-sized raw uint8 images
 resident in HBM (device pool cache), resize + z-score statistics on the GPU per 128-image chunk.
 
-    python tools/config_bench.py [--pool 100000] [--configs 1,3,4,p]
+    python tools/config_bench.py [--pool 100000] [--configs 1,3,4,p,k,b]
 """
 import argparse
 import json
@@ -86,6 +86,23 @@ def main():
             dt, names = timed(lambda: sel.select_next_batch(ad, 500, model, dev), reps=1)
             out.append({"config": 4, "what": f"hybrid entropy top-5000 -> k-center, K=3, {args.pool}-image pool, budget 500",
                         "seconds": dt, "images_per_s": args.pool / dt, "selected": len(set(names))})
+        elif c == "k":
+            model = OracleUNet(golden_state_dict(3, g))
+            ad = active(pool_u8(args.pool + 500, dev), 500)
+            sel = b200al.B200KMeanSelector(metric="cosine", **kw)
+            np.random.seed(0)
+            dt, names = timed(lambda: sel.select_next_batch(ad, 500, model, dev), reps=1)
+            out.append({"config": "k", "what": f"kmean-cosine (k-means++ seeding), K=3, {args.pool}-image pool, 500 labeled, budget 500",
+                        "seconds": dt, "images_per_s": args.pool / dt, "selected": len(set(names))})
+        elif c == "b":
+            model = OracleUNet(golden_state_dict(3, g))
+            n = min(args.pool, 10_000)
+            ad = active(pool_u8(n + 32, dev), 32)
+            sel = b200al.B200BADGESelector(**kw)
+            np.random.seed(0)
+            dt, names = timed(lambda: sel.select_next_batch(ad, 100, model, dev), reps=1)
+            out.append({"config": "b", "what": f"badge (gradient embedding + k-means++), K=3, {n}-image pool, budget 100",
+                        "seconds": dt, "images_per_s": n / dt, "selected": len(set(names))})
         elif c == "p":
             model = OracleUNet(golden_state_dict(3, g))
             n = min(args.pool, 10_000)
