@@ -325,6 +325,8 @@ class B200KMeanSelector(_B200Base):
 
     The random numbers come from numpy's GLOBAL RandomState in sklearn's call order (one `choice`, then
     `uniform(size=2+int(log k))` per further centre), so a seeded run consumes the same stream as the reference.
+    `feature_dict` + `loaded_feature_only=True` (the demo's model-free mode, entry/demo/serve.py:125-134, with e.g.
+    BiomedCLIP features per case name) replaces the embeddings by the given rows (:86-90, 101-112).
     Embedding, standardisation, pool-to-labeled distances and the whole seeding loop run on the GPU; the O(n)
     weight normalisation and the draws stay on the host in the reference's own numpy / torch calls.  Names are
     returned in pick order, duplicates dropped (the reference returns `list(set(...))`, :194).  Without labeled data
@@ -339,12 +341,29 @@ class B200KMeanSelector(_B200Base):
             raise NotImplementedError(f"metric {metric!r}: only 'l2' and 'cosine' are supported")
         if coreset_criteria not in ("min", "mean"):
             raise RuntimeError(f"coreset_criteria {coreset_criteria} is undefined")
-        if feature_path is not None or feature_dict is not None or loaded_feature_only:
-            raise NotImplementedError("externally loaded features (feature_path / feature_dict / loaded_feature_only) "
-                                      "are not supported")
+        if feature_path is not None:
+            raise NotImplementedError("feature_path (per-case .h5 files) is not supported: h5py is not available")
+        if (feature_dict is not None) != bool(loaded_feature_only):
+            # Mixing model and loaded features scales the latter by the numpy scalar np.sqrt(D1 / D2 * w) (:113-116):
+            # float32 under the reference's pinned numpy < 2, float64 under numpy 2 - the result dtype of the whole
+            # selection depends on the numpy version, so only the unambiguous combination is offered.
+            raise NotImplementedError("loaded features are supported as feature_dict together with "
+                                      "loaded_feature_only=True (the model-free mode of the demo)")
+        self.feature_dict, self.loaded_feature_only = feature_dict, bool(loaded_feature_only)
         self.metric, self.coreset_criteria = metric, coreset_criteria
         self.sharp_factor, self.softmax = sharp_factor, bool(softmax)
         self.loaded_feature_weight = loaded_feature_weight
+
+    def _loaded_rows(self, eng: Engine, names) -> torch.Tensor:
+        """Rows of `feature_dict` for `names`, standardised per row (:101-105) and zero-padded to the next supported
+        width (128 / 256 / 512 / 1024 columns; padding changes neither l2 nor cosine distances)."""
+        import numpy as np
+        rows = np.stack([np.asarray(self.feature_dict[n], dtype=np.float32).reshape(-1) for n in names], axis=0)
+        x = eng.standardize_rows(torch.from_numpy(rows).to(eng.device))
+        width = next((w for w in (128, 256, 512, 1024) if w >= x.shape[1]), None)
+        if width is None:
+            raise NotImplementedError(f"loaded features of dimension {x.shape[1]} (> 1024) are not supported")
+        return torch.nn.functional.pad(x, (0, width - x.shape[1])) if width != x.shape[1] else x
 
     def select_next_batch(self, active_dataset, select_num: int, model, device):
         import numpy as np
@@ -355,13 +374,20 @@ class B200KMeanSelector(_B200Base):
             raise ValueError(f"n_samples={pool_size} should be >= n_clusters={select_num}.")
         labeled, pool = active_dataset.get_train_dataset(), active_dataset.get_pool_dataset()
         rank, ws = D.world()
-        lo, hi = D.shard_range(pool_size, rank, ws)
-        psrc = self._source(pool, device)
-        eng = self._engine(model, device, psrc.image_hw())
-        X = eng.standardize_rows(D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi)))))
-        if labeled_size > 0:
-            lsrc = self._source(labeled, device)
-            Xl = eng.standardize_rows(_embed_positions(eng, lsrc, list(range(labeled_size))))
+        if self.loaded_feature_only:
+            eng = get_engine(device, 2, 256, 256, self.precision, 1)  # kernels only; no model involved
+            X = self._loaded_rows(eng, pool.image_idx)
+            Xl = self._loaded_rows(eng, labeled.image_idx) if labeled_size > 0 else None
+        else:
+            lo, hi = D.shard_range(pool_size, rank, ws)
+            psrc = self._source(pool, device)
+            eng = self._engine(model, device, psrc.image_hw())
+            X = eng.standardize_rows(D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi)))))
+            Xl = None
+            if labeled_size > 0:
+                lsrc = self._source(labeled, device)
+                Xl = eng.standardize_rows(_embed_positions(eng, lsrc, list(range(labeled_size))))
+        if Xl is not None:
             w = eng.centre_distances(X, Xl, self.metric, self.coreset_criteria).cpu()
             if self.softmax:  # kmean_selector.py:180-183
                 w = (w * self.sharp_factor).softmax(0).numpy()

@@ -34,7 +34,19 @@ CASES = [
     ("K3/l2/cold", 3, 0, 64, 8, dict(metric="l2")),
     ("K2/l2/min", 2, 32, 128, 16, dict(metric="l2")),
     ("K2/cosine/min/sharp2", 2, 32, 128, 16, dict(metric="cosine", sharp_factor=2.0)),
+    # the demo's model-free mode (entry/demo/serve.py:125-134): features come from a dict, the model is not used
+    ("dict/l2/min", 3, 12, 60, 10, dict(metric="l2", loaded_feature_only=True)),
+    ("dict/cosine/mean", 3, 12, 60, 10, dict(metric="cosine", coreset_criteria="mean", loaded_feature_only=True)),
 ]
+DICT_DIM, DICT_SEED = 200, 99
+
+
+def loaded_features(names) -> dict:
+    """Seeded stand-in for foundation-model features: one fp32 row of DICT_DIM per case name."""
+    rng = np.random.default_rng(DICT_SEED)
+    base = rng.standard_normal((8, DICT_DIM))
+    return {n: (base[i % 8] * (1 + 0.3 * rng.standard_normal()) + 0.5 * rng.standard_normal(DICT_DIM)).astype(np.float32)
+            for i, n in enumerate(names)}
 
 
 def main():
@@ -50,11 +62,16 @@ def main():
             m.load_state_dict(golden_state_dict(K, g))
             models[K] = m
         ad = make_active(synth_pool_u8(n_lab + n_pool), n_lab, reference=ref)
-        sel = ref.KMeanSelector(batch_size=8, num_workers=0, pin_memory=False, **kw)
+        all_names = list(ad.get_train_dataset().image_idx) + list(ad.get_pool_dataset().image_idx)
+        fd = loaded_features(all_names) if kw.get("loaded_feature_only") else None
+        sel = ref.KMeanSelector(batch_size=8, num_workers=0, pin_memory=False, feature_dict=fd, **kw)
         np.random.seed(NP_SEED)
-        names = sel.select_next_batch(ad, budget, models[K], torch.device("cpu"))
+        names = sel.select_next_batch(ad, budget, None if fd else models[K], torch.device("cpu"))
         out[key] = np.array(sorted(map(str, names)))
-        emb = S.pool_embeddings(golden_state_dict(K, g), synth_pool_u8(n_lab + n_pool))
+        if fd:
+            emb = np.stack([fd[n] for n in all_names])
+        else:
+            emb = S.pool_embeddings(golden_state_dict(K, g), synth_pool_u8(n_lab + n_pool))
         idx, gap = kmean_select(emb[n_lab:], emb[:n_lab] if n_lab else None, budget, kw.get("metric", "cosine"),
                                 kw.get("coreset_criteria", "min"), kw.get("sharp_factor", 1.0), kw.get("softmax", False),
                                 np.random.RandomState(NP_SEED), return_gap=True)

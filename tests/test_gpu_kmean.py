@@ -76,18 +76,20 @@ def test_kmeans_pp_kernels_pick_sklearns_indices():
 
 def test_kmean_selector_matches_reference_golden(golden):
     """The drop-in selector end to end (embeddings from the tcgen05 encoder) vs the reference KMeanSelector's frozen
-    selections, all eight cases (l2 / cosine, min / mean, sharp_factor, softmax, no labeled data)."""
+    selections, all ten cases (l2 / cosine, min / mean, sharp_factor, softmax, no labeled data, feature_dict mode)."""
     import b200al
-    from oracle.make_golden_kmean import CASES
-    from oracle.synth import make_active, synth_pool_u8
+    from oracle.make_golden_kmean import CASES, loaded_features
+    from oracle.synth import case_name, make_active, synth_pool_u8
     from oracle.unet_ref import OracleUNet, golden_state_dict
     gk = np.load(os.path.join(os.path.dirname(__file__), "golden", "kmean.npz"))
     models = {K: OracleUNet(golden_state_dict(K, golden["model"])) for K in (2, 3)}
     for key, K, n_lab, n_pool, budget, kw in CASES:
         ad = make_active(synth_pool_u8(n_lab + n_pool), n_lab)
-        sel = b200al.B200KMeanSelector(batch_size=8, num_workers=0, pin_memory=False, **kw)
+        # the demo's model-free mode: features per case name from a dict (200 columns -> padded to 256), no model
+        fd = loaded_features([case_name(i) for i in range(n_lab + n_pool)]) if kw.get("loaded_feature_only") else None
+        sel = b200al.B200KMeanSelector(batch_size=8, num_workers=0, pin_memory=False, feature_dict=fd, **kw)
         np.random.seed(int(gk["np_seed"]))
-        names = sel.select_next_batch(ad, budget, models[K], torch.device(DEV))
+        names = sel.select_next_batch(ad, budget, None if fd else models[K], torch.device(DEV))
         assert len(names) == len(set(names)) and set(names) <= set(ad.get_pool_dataset().image_idx)
         assert sorted(names) == gk[key].tolist(), key
     # the numpy stream advanced exactly as far as sklearn advances it: 1 choice + (k-1) * trials uniforms
@@ -106,6 +108,8 @@ def test_kmean_selector_contract_and_registry():
         b200al.B200KMeanSelector(batch_size=1, num_workers=0, metric="l1")
     with pytest.raises(NotImplementedError):
         b200al.B200KMeanSelector(batch_size=1, num_workers=0, feature_path="/tmp/x")
+    with pytest.raises(NotImplementedError):  # mixing model and loaded features: result dtype depends on the numpy version
+        b200al.B200KMeanSelector(batch_size=1, num_workers=0, feature_dict={"a": [1.0, 2.0]})
     with pytest.raises(RuntimeError):
         b200al.B200KMeanSelector(batch_size=1, num_workers=0, coreset_criteria="median")
     s = b200al.SELECTORS["b200-kmean-l2"](batch_size=2, num_workers=0, pin_memory=False)
