@@ -1112,16 +1112,17 @@ extern "C" int b200al_standardize_rows(b200al_ctx* ctx, const float* d_in, float
 extern "C" size_t b200al_kmeans_pp_scratch_bytes(int n, int n_local_trials) {
   if (n < 1 || n_local_trials < 1) return 0;
   const size_t blocks = 148 * 8;
-  return ((size_t)n * (n_local_trials + 1)) * sizeof(float) + blocks * n_local_trials * sizeof(double) + 256;
+  return ((size_t)n * (n_local_trials + 1)) * sizeof(float) + blocks * n_local_trials * sizeof(double) + 256 +
+         (size_t)n * sizeof(double) + 16;
 }
 
 namespace {
 template <int NV>
-void launch_kmpp_dist(const float* X, const float* w, int n, const int* cand, int trials, const float* closest, int first,
-                      float* cand_d, double* part, int blocks, cudaStream_t st) {
-  const size_t smem = (size_t)trials * NV * 128 * sizeof(float);
+void launch_kmpp_dist(const float* X, const double* xx, const float* w, int n, const int* cand, int trials,
+                      const float* closest, int first, float* cand_d, double* part, int blocks, cudaStream_t st) {
+  const size_t smem = (size_t)trials * NV * 128 * sizeof(double);
   cudaFuncSetAttribute(kmpp_dist_kernel<NV>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  kmpp_dist_kernel<NV><<<blocks, 256, smem, st>>>(X, w, n, cand, trials, closest, first, cand_d, part);
+  kmpp_dist_kernel<NV><<<blocks, 256, smem, st>>>(X, xx, w, n, cand, trials, closest, first, cand_d, part);
 }
 }  // namespace
 
@@ -1151,13 +1152,24 @@ extern "C" int b200al_kmeans_pp(b200al_ctx* ctx, const float* d_X, int n, int D,
   float* pot = (float*)((char*)d_scratch + off);
   int* best = (int*)(pot + 1);
   int* cand = best + 1;
+  off = (off + 256 + 15) & ~(size_t)15;
+  double* xx = (double*)((char*)d_scratch + off);  // [n] squared row norms
   long long* picks = (long long*)d_picks;
+  if ((size_t)trials * D * sizeof(double) > 200 * 1024)
+    return set_err(ctx, B200AL_ERR_ARG, "n_local_trials * D too large for the candidate tile");
+  switch (D / 128) {
+    case 1: kmpp_norms_kernel<1><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
+    case 2: kmpp_norms_kernel<2><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
+    case 4: kmpp_norms_kernel<4><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
+    case 8: kmpp_norms_kernel<8><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
+  }
+  ctx->launches++;
 #define KMPP_DIST(TR, FIRST)                                                                                   \
   switch (D / 128) {                                                                                           \
-    case 1: launch_kmpp_dist<1>(d_X, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
-    case 2: launch_kmpp_dist<2>(d_X, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
-    case 4: launch_kmpp_dist<4>(d_X, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
-    case 8: launch_kmpp_dist<8>(d_X, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 1: launch_kmpp_dist<1>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 2: launch_kmpp_dist<2>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 4: launch_kmpp_dist<4>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 8: launch_kmpp_dist<8>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
   }
   kmpp_set_first_kernel<<<1, 1, 0, st>>>(cand, first_centre);
   KMPP_DIST(1, 1)
@@ -1167,7 +1179,7 @@ extern "C" int b200al_kmeans_pp(b200al_ctx* ctx, const float* d_X, int n, int D,
   for (int c = 1; c < n_clusters; ++c) {
     kmpp_sample_kernel<<<1, 1024, 0, st>>>(d_weight, closest, n, d_uniform + (size_t)(c - 1) * trials, trials, pot, cand);
     KMPP_DIST(trials, 0)
-    kmpp_pick_kernel<<<1, 32, 0, st>>>(part, blocks, cand, trials, pot, best, picks + c);
+    kmpp_pick_kernel<<<1, 32 * trials, 0, st>>>(part, blocks, cand, trials, pot, best, picks + c);
     kmpp_commit_kernel<<<blocks, 256, 0, st>>>(cand_d, best, n, closest);
     ctx->launches += 4;
   }

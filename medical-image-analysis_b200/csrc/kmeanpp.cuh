@@ -7,8 +7,9 @@
 //   1. kmpp_sample_kernel   cum = cumsum_f32(w * closest) strictly SEQUENTIAL in fp32 (numpy's accumulate order: the
 //                           candidate indices depend on its rounding), candidates = searchsorted(cum, u * pot), clipped.
 //                           The chain runs in one thread over shared-memory chunks the rest of the CTA loads and scans.
-//   2. kmpp_dist_kernel     d[t][i] = min(closest[i], f32(sum_k (x_ik - c_tk)^2 in fp64)) for the <= 16 candidates,
-//                           one warp per row, candidates resident in shared memory; weighted potentials in fp64 per CTA.
+//   2. kmpp_dist_kernel     d[t][i] = min(closest[i], f32(max(xx_i + cc_t - 2 x_i.c_t, 0) in fp64)) for the <= 16
+//                           candidates, one warp per row, candidates resident in shared memory as doubles; weighted
+//                           potentials in fp64 per CTA.  (The vector fp64 rate is what bounds this kernel.)
 //   3. kmpp_pick_kernel     potentials reduced in fixed order, rounded to fp32; first minimum wins.
 //   4. kmpp_commit_kernel   closest = d[best].
 // sklearn evaluates the potentials with an fp32 BLAS dot of CPU-specific summation order; fp64-then-fp32 here agrees
@@ -48,13 +49,15 @@ __global__ void standardize_rows_kernel(const float* __restrict__ in, float* __r
 __global__ void __launch_bounds__(1024)
 kmpp_sample_kernel(const float* __restrict__ w, const float* __restrict__ closest, int n, const double* __restrict__ u,
                    int trials, const float* __restrict__ pot, int* __restrict__ cand) {
-  __shared__ float buf[kKmppChunk];
+  __shared__ __align__(16) float buf[kKmppChunk];
   __shared__ int cnt[kKmppMaxTrials];
   __shared__ float carry_s;
-  double r[kKmppMaxTrials];
+  // searchsorted compares (double)cum[i] < u*pot; for an fp32 cum[i] that is cum[i] < (u*pot rounded UP to fp32),
+  // which keeps the fp64 pipe out of the scan
+  float r[kKmppMaxTrials];
   const double p = (double)pot[0];
 #pragma unroll
-  for (int t = 0; t < kKmppMaxTrials; ++t) r[t] = t < trials ? u[t] * p : 0.0;
+  for (int t = 0; t < kKmppMaxTrials; ++t) r[t] = t < trials ? __double2float_ru(u[t] * p) : 0.f;
   int local[kKmppMaxTrials];
 #pragma unroll
   for (int t = 0; t < kKmppMaxTrials; ++t) local[t] = 0;
@@ -68,15 +71,31 @@ kmpp_sample_kernel(const float* __restrict__ w, const float* __restrict__ closes
     if (threadIdx.x == 0) {
       float c = carry_s;
       int j = 0;
+      // the dependent fp32 add (4 cycles) is the floor: 128-bit shared-memory accesses (12 instructions per 8
+      // elements instead of 24) and the next 8 elements fetched before the current adds (hides the LDS latency)
+      float4 a, b;
+      if (m >= 8) {
+        a = *reinterpret_cast<const float4*>(buf);
+        b = *reinterpret_cast<const float4*>(buf + 4);
+      }
       for (; j + 8 <= m; j += 8) {
-        float v[8];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) v[q] = buf[j + q];
-#pragma unroll
-        for (int q = 0; q < 8; ++q) {
-          c = __fadd_rn(c, v[q]);
-          buf[j + q] = c;
+        float4 na = a, nb = b;
+        if (j + 16 <= m) {
+          na = *reinterpret_cast<const float4*>(buf + j + 8);
+          nb = *reinterpret_cast<const float4*>(buf + j + 12);
         }
+        c = __fadd_rn(c, a.x); a.x = c;
+        c = __fadd_rn(c, a.y); a.y = c;
+        c = __fadd_rn(c, a.z); a.z = c;
+        c = __fadd_rn(c, a.w); a.w = c;
+        c = __fadd_rn(c, b.x); b.x = c;
+        c = __fadd_rn(c, b.y); b.y = c;
+        c = __fadd_rn(c, b.z); b.z = c;
+        c = __fadd_rn(c, b.w); b.w = c;
+        *reinterpret_cast<float4*>(buf + j) = a;
+        *reinterpret_cast<float4*>(buf + j + 4) = b;
+        a = na;
+        b = nb;
       }
       for (; j < m; ++j) {
         c = __fadd_rn(c, buf[j]);
@@ -86,7 +105,7 @@ kmpp_sample_kernel(const float* __restrict__ w, const float* __restrict__ closes
     }
     __syncthreads();
     for (int j = threadIdx.x; j < m; j += blockDim.x) {
-      const double v = (double)buf[j];
+      const float v = buf[j];
 #pragma unroll
       for (int t = 0; t < kKmppMaxTrials; ++t)
         if (t < trials) local[t] += v < r[t] ? 1 : 0;
@@ -104,15 +123,45 @@ kmpp_sample_kernel(const float* __restrict__ w, const float* __restrict__ closes
   if (threadIdx.x < trials) cand[threadIdx.x] = min(cnt[threadIdx.x], n - 1);
 }
 
-// grid-stride over rows, one warp per row; dynamic smem = trials * D floats (candidate rows)
+// xx[i] = sum_k x_ik^2 in fp64 (once per call)
+template <int NV>
+__global__ void __launch_bounds__(256) kmpp_norms_kernel(const float* __restrict__ X, int n, double* __restrict__ xx) {
+  constexpr int D = NV * 128;
+  const int lane = threadIdx.x & 31;
+  const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int row = warp_global; row < n; row += nwarps) {
+    float4 x[NV];
+    load_row<NV>(X + (size_t)row * D, lane, x);
+    double acc = 0.0;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      acc = fma((double)x[j].x, (double)x[j].x, acc); acc = fma((double)x[j].y, (double)x[j].y, acc);
+      acc = fma((double)x[j].z, (double)x[j].z, acc); acc = fma((double)x[j].w, (double)x[j].w, acc);
+    }
+    acc = warp_sum_f64(acc);
+    if (lane == 0) xx[row] = acc;
+  }
+}
+
+// grid-stride over rows, one warp per row; dynamic smem = trials * D doubles (candidate rows, converted once per CTA).
+// d = xx + cc - 2 x.c evaluated in fp64 - sklearn's own formula (`_euclidean_distances_upcast`) and half the fp64
+// work of summing (x - c)^2; a row's distance to itself is forced to 0.
 template <int NV>
 __global__ void __launch_bounds__(256)
-kmpp_dist_kernel(const float* __restrict__ X, const float* __restrict__ w, int n, const int* __restrict__ cand, int trials,
-                 const float* __restrict__ closest, int first, float* __restrict__ cand_d, double* __restrict__ part) {
-  extern __shared__ float kc[];  // [trials][D]
+kmpp_dist_kernel(const float* __restrict__ X, const double* __restrict__ xx, const float* __restrict__ w, int n,
+                 const int* __restrict__ cand, int trials, const float* __restrict__ closest, int first,
+                 float* __restrict__ cand_d, double* __restrict__ part) {
+  extern __shared__ double kc[];  // [trials][D]
   constexpr int D = NV * 128;
   __shared__ double red[8][kKmppMaxTrials];
-  for (int i = threadIdx.x; i < trials * D; i += blockDim.x) kc[i] = X[(size_t)cand[i / D] * D + (i % D)];
+  __shared__ double cc[kKmppMaxTrials];
+  __shared__ int cid[kKmppMaxTrials];
+  for (int i = threadIdx.x; i < trials * D; i += blockDim.x) kc[i] = (double)X[(size_t)cand[i / D] * D + (i % D)];
+  if (threadIdx.x < trials) {
+    cid[threadIdx.x] = cand[threadIdx.x];
+    cc[threadIdx.x] = xx[cand[threadIdx.x]];
+  }
   __syncthreads();
   const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -121,23 +170,30 @@ kmpp_dist_kernel(const float* __restrict__ X, const float* __restrict__ w, int n
 #pragma unroll
   for (int t = 0; t < kKmppMaxTrials; ++t) pot[t] = 0.0;
   for (int row = warp_global; row < n; row += nwarps) {
-    float4 x[NV];
-    load_row<NV>(X + (size_t)row * D, lane, x);
+    float4 xf[NV];
+    load_row<NV>(X + (size_t)row * D, lane, xf);
+    double x[NV][4];
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      x[j][0] = (double)xf[j].x; x[j][1] = (double)xf[j].y; x[j][2] = (double)xf[j].z; x[j][3] = (double)xf[j].w;
+    }
     const float cur = first ? CUDART_INF_F : closest[row];
-    const double wr = (double)w[row];
+    const double wr = (double)w[row], xr = xx[row];
 #pragma unroll
     for (int t = 0; t < kKmppMaxTrials; ++t) {
       if (t < trials) {
-        double acc = 0.0;
+        double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;  // four independent chains: the fp64 FMA latency is long
 #pragma unroll
         for (int j = 0; j < NV; ++j) {
-          const float4 c = *reinterpret_cast<const float4*>(kc + t * D + (j * 32 + lane) * 4);
-          const double d0 = (double)x[j].x - (double)c.x, d1 = (double)x[j].y - (double)c.y;
-          const double d2 = (double)x[j].z - (double)c.z, d3 = (double)x[j].w - (double)c.w;
-          acc = fma(d0, d0, acc); acc = fma(d1, d1, acc); acc = fma(d2, d2, acc); acc = fma(d3, d3, acc);
+          const double2 c01 = *reinterpret_cast<const double2*>(kc + t * D + (j * 32 + lane) * 4);
+          const double2 c23 = *reinterpret_cast<const double2*>(kc + t * D + (j * 32 + lane) * 4 + 2);
+          a0 = fma(x[j][0], c01.x, a0); a1 = fma(x[j][1], c01.y, a1);
+          a2 = fma(x[j][2], c23.x, a2); a3 = fma(x[j][3], c23.y, a3);
         }
-        acc = warp_sum_f64(acc);
-        const float m = fminf(cur, (float)acc);
+        double acc = warp_sum_f64((a0 + a1) + (a2 + a3));
+        double d = xr + cc[t] - 2.0 * acc;
+        if (row == cid[t] || d < 0.0) d = 0.0;
+        const float m = fminf(cur, (float)d);
         if (lane == 0) cand_d[(size_t)t * n + row] = m;
         pot[t] = fma(wr, (double)m, pot[t]);
       }
@@ -155,20 +211,20 @@ kmpp_dist_kernel(const float* __restrict__ X, const float* __restrict__ w, int n
   }
 }
 
-// <<<1, 32>>>
+// <<<1, 32 * trials>>>: warp t reduces the partials of trial t (lane-strided sums, then a fixed shuffle tree)
 __global__ void kmpp_pick_kernel(const double* __restrict__ part, int blocks, const int* __restrict__ cand, int trials,
                                  float* __restrict__ pot, int* __restrict__ best, long long* __restrict__ pick_out) {
   __shared__ float pots[kKmppMaxTrials];
-  if ((int)threadIdx.x < trials) {
-    double s = 0.0;
-    for (int b = 0; b < blocks; ++b) s += part[(size_t)threadIdx.x * blocks + b];
-    pots[threadIdx.x] = (float)s;
-  }
+  const int t = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  double s = 0.0;
+  for (int b = lane; b < blocks; b += 32) s += part[(size_t)t * blocks + b];
+  s = warp_sum_f64(s);
+  if (lane == 0) pots[t] = (float)s;
   __syncthreads();
   if (threadIdx.x == 0) {
     int b = 0;
-    for (int t = 1; t < trials; ++t)
-      if (pots[t] < pots[b]) b = t;  // np.argmin: first minimum
+    for (int q = 1; q < trials; ++q)
+      if (pots[q] < pots[b]) b = q;  // np.argmin: first minimum
     pot[0] = pots[b];
     best[0] = b;
     pick_out[0] = cand[b];
