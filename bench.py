@@ -172,6 +172,33 @@ def run_reference(args):
     }))
 
 
+def ncu_traffic():
+    """DRAM bytes per launch (read + write) from the committed `ncu --set full` summaries of the same kernels at the
+    bench's chunk size (profiles/r01_ncu_full_conv_v9.csv: the conv launches of one 128-sample chunk;
+    profiles/r01_ncu_full_uncertainty_v9.csv: 16 images x T=8 per launch).  None when the files are absent."""
+    import csv
+    here = os.path.dirname(os.path.abspath(__file__))
+
+    def rows(name):
+        path = os.path.join(here, "profiles", name)
+        if not os.path.exists(path):
+            return []
+        with open(path) as f:
+            return list(csv.DictReader(f))
+
+    def total(r):
+        out = 0.0
+        for k, v in r.items():
+            if k.startswith("dram__bytes_read.sum") or k.startswith("dram__bytes_write.sum"):
+                unit = k[k.index("[") + 1:k.index("]")]
+                out += float(v) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[unit]
+        return out
+
+    conv = [total(r) for r in rows("r01_ncu_full_conv_v9.csv")]
+    unc = [total(r) for r in rows("r01_ncu_full_uncertainty_v9.csv")]
+    return (sum(conv) / len(conv) if conv else None), (sum(unc) / len(unc) / 16 if unc else None)
+
+
 def workload_name(args):
     return (f"UNet MC-dropout (T={T_REPEATS}) entropy acquisition, FUGC-shape 1x256x256 K={K_CLASSES}, "
             f"{args.pool}-image synthetic pool per GPU, budget {BUDGET}")
@@ -294,6 +321,7 @@ def run_b200(args):
         tf_peak, hbm_peak, peak_src = peaks()
         value = world * n * args.steps / (ms / 1e3)
         achieved = conv_fl / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
+        conv_traffic, unc_traffic_per_image = ncu_traffic()
         line = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
@@ -307,7 +335,9 @@ def run_b200(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
-                         "frac": achieved / tf_peak, "traffic": None,
+                         "frac": achieved / tf_peak, "traffic": conv_traffic,
+                         "traffic_note": "mean DRAM read+write bytes per conv launch of a 128-sample chunk, ncu --set full "
+                                         "(profiles/r01_ncu_full_conv_v9.csv); tensor-bound kernels, shown for completeness",
                          "kernel": "conv_fold_kernel + conv_tc_kernel (tcgen05 implicit GEMM, the 21 conv/convT layers)",
                          "launches_timed": int(conv_n), "avg_launch_ms": conv_ms / max(conv_n, 1),
                          "flops_note": "algorithmic 2*MAC of the fp32 reference conv; bf16x3 issues 3 MMAs per product, "
@@ -317,7 +347,11 @@ def run_b200(args):
         }
         if unc:
             line["roofline_hbm_kernel"] = {"bound": "hbm", "achieved": unc[0], "peak": hbm_peak, "unit": "GB/s",
-                                           "frac": unc[0] / hbm_peak, "traffic": None,
+                                           "frac": unc[0] / hbm_peak,
+                                           "traffic": unc_traffic_per_image * 128 if unc_traffic_per_image else None,
+                                           "traffic_note": "ncu --set full DRAM read+write bytes per image x 128 images "
+                                                           "(profiles/r01_ncu_full_uncertainty_v9.csv); algorithmic = "
+                                                           "bytes_per_launch",
                                            "kernel": "uncertainty_logits_kernel (softmax + entropy + per-image mean, "
                                                      "128 images x T=8 x K=3 fp32 logits)",
                                            "avg_launch_ms": unc[1], "bytes_per_launch": unc[2],
