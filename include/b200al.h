@@ -153,6 +153,16 @@ int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, int D, const
  * d_state / d_taken are updated in place. */
 int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, int criteria, int n_centres,
                        void* d_state, uint8_t* d_taken, int budget, int64_t* d_picks, float* d_pick_vals, void* stream);
+/* CoresetSelector with externally loaded features, coreset_fusion="add" (coreset_selector.py:110-157, 221-229):
+ * k-center greedy on  loaded_weight * D_loaded / sum(D_loaded) + emb_weight * D_emb / sum(D_emb)  (emb_weight =
+ * fl32(1 - w) computed by the caller in double like the reference's python expression) over rows 0..n-1 of the two
+ * feature matrices d_emb [n,D1] (D1 <= 1024) and d_loaded [n,D2] (any width); rows 0..n_init-1 are the labeled set.
+ * The two global pair-distance sums are computed on the device (one O(n^2) pass each, no n x n matrix).
+ * d_picks [budget] int64 in selection order (-1 when exhausted), d_pick_vals nullable.  Synchronises the stream. */
+int b200al_kcenter_fused(b200al_ctx* ctx, const float* d_emb, int D1, const float* d_loaded, int D2, int n, int n_init,
+                         int metric, int criteria, float loaded_weight, float emb_weight, int budget,
+                         int64_t* d_picks, float* d_pick_vals, void* stream);
+
 /* KMeanSelector (kmean_selector.py:19-196).
  * standardize_rows: (x - mean) / std per row, population std (:95-97).
  * kmeans_pp: scikit-learn's weighted k-means++ seeding (`kmeans_plusplus`, kmean_selector.py:190-192; sklearn 1.9.0

@@ -54,6 +54,8 @@ PROTOTYPES = {
     "b200al_load_weights": (C.c_int, [C.c_void_p, C.POINTER(Weights), C.c_void_p]),
     "b200al_prep_images": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                      C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200al_kcenter_fused": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+                                       C.c_int, C.c_float, C.c_float, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200al_standardize_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "b200al_kmeans_pp_scratch_bytes": (C.c_size_t, [C.c_int, C.c_int]),
     "b200al_kmeans_pp": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_int,

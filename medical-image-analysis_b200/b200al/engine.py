@@ -339,6 +339,31 @@ class Engine:
                                                     self._ptr(taken), budget, self._ptr(picks), self._ptr(vals), st))
         return (picks, vals) if return_vals else picks
 
+    def kcenter_fused(self, feats: torch.Tensor, loaded: torch.Tensor, loaded_weight: float, n_init: int, budget: int,
+                      metric: str = "l2", criteria: str = "min", return_vals: bool = False):
+        """k-center greedy on `w * D_loaded / sum(D_loaded) + (1 - w) * D_feats / sum(D_feats)` - CoresetSelector
+        with externally loaded features and coreset_fusion="add" (coreset_selector.py:138-157).  Rows [0, n_init) of
+        both matrices are the labeled set.  Row indices (int64, selection order)."""
+        feats = feats.to(device=self.device, dtype=torch.float32).contiguous()
+        loaded = loaded.to(device=self.device, dtype=torch.float32).contiguous()
+        n = feats.shape[0]
+        if loaded.shape[0] != n:
+            raise ValueError("feats and loaded must have the same number of rows")
+        if n_init < 1:
+            raise ValueError("k-center needs at least one labeled row")
+        if criteria not in _lib.CRITERIA:
+            raise RuntimeError(f"coreset_criteria {criteria} is undefined")
+        budget = min(int(budget), n - n_init)
+        picks = torch.empty(budget, dtype=torch.int64, device=self.device)
+        vals = torch.empty(budget, dtype=torch.float32, device=self.device)
+        if budget > 0:
+            with torch.cuda.device(self.device):
+                self._check(self.lib.b200al_kcenter_fused(
+                    self.ctx, self._ptr(feats), feats.shape[1], self._ptr(loaded), loaded.shape[1], n, int(n_init),
+                    _lib.METRICS[metric], _lib.CRITERIA[criteria], float(loaded_weight), float(1 - loaded_weight),
+                    budget, self._ptr(picks), self._ptr(vals), self._stream()))
+        return (picks, vals) if return_vals else picks
+
     def centre_distances(self, feats: torch.Tensor, centres: torch.Tensor, metric: str = "l2",
                          criteria: str = "min") -> torch.Tensor:
         """Per row of `feats` [n,D]: min (or mean) over the rows of `centres` [L,D] of the sklearn-fp32 distance -

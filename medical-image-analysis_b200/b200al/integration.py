@@ -27,6 +27,8 @@ def install_into_al_trainer(trainer_cls, reference_abc=None):
             if name.startswith("b200-coreset"):  # al_trainer.py:823-844 forwards these two to CoresetSelector
                 kw["coreset_criteria"] = getattr(self.config, "coreset_criteria", "min")
                 kw["coreset_fusion"] = getattr(self.config, "coreset_fusion", "add")
+                kw["feature_path"] = getattr(self.config, "feature_path", None)
+                kw["loaded_feature_weight"] = getattr(self.config, "loaded_feature_weight", 0.0)
             if name.startswith("b200-kmean"):  # al_trainer.py:845-870
                 kw["coreset_criteria"] = getattr(self.config, "coreset_criteria", "min")
                 kw["sharp_factor"] = getattr(self.config, "kmean_sharp_factor", 1.0)

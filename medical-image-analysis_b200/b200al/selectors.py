@@ -283,28 +283,79 @@ def _embed_positions(eng: Engine, src: PoolSource, positions: list[int]) -> torc
     return out
 
 
+def _loaded_feature_rows(names, feature_dict=None, feature_path=None):
+    """[len(names), D2] float32 array of externally loaded (foundation-model) features: rows of `feature_dict`, or
+    the `feature` dataset of `{feature_path}/{case}.h5` (coreset_selector.py:110-119; needs h5py)."""
+    import numpy as np
+    if feature_dict is not None:
+        return np.stack([np.asarray(feature_dict[n], dtype=np.float32).reshape(-1) for n in names], axis=0)
+    import h5py  # the reference's own dependency
+    rows = []
+    for n in names:
+        with h5py.File(feature_path / f"{n}.h5", "r") as h5f:
+            rows.append(np.asarray(h5f["feature"][:], dtype=np.float32).reshape(-1))
+    return np.stack(rows, axis=0)
+
+
 class B200CoresetSelector(_B200Base):
-    """CoresetSelector (src/activelearning/coreset_selector.py:54) for
-    metric in {l2, cosine}, coreset_criteria in {min, mean}, model features only."""
+    """CoresetSelector (src/activelearning/coreset_selector.py:54) for metric in {l2, cosine}, coreset_criteria in
+    {min, mean}; model features alone, or fused with externally loaded features by coreset_fusion="add"
+    (:138-157: each distance matrix divided by its global sum, mixed with `loaded_feature_weight`).  Loaded features
+    come from `feature_path` (`{case}.h5`, needs h5py like the reference) or from `feature_dict` (case name -> row;
+    an extension for callers that already hold them in memory, like KMeanSelector's).  coreset_fusion="cat" with loaded
+    features is not offered: it scales them by a numpy scalar (:170), so the dtype of the whole selection depends on
+    the numpy version."""
 
     def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8,
                  metric: str = "cosine", coreset_criteria: str = "min", coreset_fusion: str = "add",
-                 feature_path=None, loaded_feature_weight: float = 0.0, **kw):
+                 feature_path=None, loaded_feature_weight: float = 0.0, feature_dict=None, **kw):
         super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
         if metric not in ("l2", "cosine"):
             raise NotImplementedError(f"metric {metric!r}: only 'l2' and 'cosine' are supported")
         if coreset_criteria not in ("min", "mean"):
             raise RuntimeError(f"coreset_criteria {coreset_criteria} is undefined")  # coreset_selector.py:38-40
-        if feature_path is not None or loaded_feature_weight != 0.0:
-            raise NotImplementedError("externally loaded features (feature_path / loaded_feature_weight) are not supported")
+        self.has_loaded = feature_path is not None or feature_dict is not None
+        if self.has_loaded and coreset_fusion != "add":
+            raise NotImplementedError("loaded features are supported with coreset_fusion='add' only")
+        if feature_path is not None and feature_dict is None:
+            try:
+                import h5py  # noqa: F401
+            except ImportError as e:
+                raise NotImplementedError("feature_path needs h5py (not installed); pass feature_dict instead") from e
+            from pathlib import Path
+            feature_path = Path(feature_path)
         self.metric = metric
         self.coreset_criteria = coreset_criteria
+        self.coreset_fusion = coreset_fusion
+        self.feature_path, self.feature_dict = feature_path, feature_dict
+        self.loaded_feature_weight = float(loaded_feature_weight)
 
     def select_next_batch(self, active_dataset, select_num: int, model, device):
+        import numpy as np
         labeled_size, pool_size = active_dataset.get_size()
-        if labeled_size == 0:
-            return _cold_start(active_dataset, select_num)  # coreset_selector.py:193-200
         labeled, pool = active_dataset.get_train_dataset(), active_dataset.get_pool_dataset()
+        if labeled_size == 0:
+            if self.loaded_feature_weight == 0 or not self.has_loaded:
+                return _cold_start(active_dataset, select_num)  # coreset_selector.py:193-200, 211-217
+            # :201-210 - k-means++ seeding over the loaded features alone, numpy's global RNG
+            if select_num <= 0:
+                return []
+            if pool_size < select_num:
+                raise ValueError(f"n_samples={pool_size} should be >= n_clusters={select_num}.")
+            eng = get_engine(device, 2, 256, 256, self.precision, 1)
+            rows = torch.from_numpy(_loaded_feature_rows(pool.image_idx, self.feature_dict, self.feature_path))
+            width = next((w for w in (128, 256, 512, 1024) if w >= rows.shape[1]), None)
+            if width is None:
+                raise NotImplementedError(f"loaded features of dimension {rows.shape[1]} (> 1024) are not supported")
+            X = torch.nn.functional.pad(rows, (0, width - rows.shape[1])).to(eng.device)
+            rs = np.random.mtrand._rand
+            trials = 2 + int(np.log(select_num))
+            w = np.ones(pool_size, dtype=np.float32)
+            first = int(rs.choice(pool_size, p=w / w.sum()))
+            uniforms = np.stack([rs.uniform(size=trials) for _ in range(select_num - 1)]) if select_num > 1 \
+                else np.zeros((0, trials))
+            picks = eng.kmeans_pp(X, torch.from_numpy(w), first, torch.from_numpy(uniforms), select_num, trials)
+            return [pool.image_idx[i] for i in picks.tolist()]
         all_list = list(labeled.image_idx) + list(pool.image_idx)  # labeled rows first (coreset_selector.py:85-88)
         rank, ws = D.world()
         lo, hi = D.shard_range(pool_size, rank, ws)
@@ -314,7 +365,12 @@ class B200CoresetSelector(_B200Base):
         emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
         emb_p = D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi))))
         feats = torch.cat([emb_l, emb_p], 0)
-        picks = eng.kcenter(feats, labeled_size, select_num, self.metric, criteria=self.coreset_criteria)
+        if self.has_loaded:
+            loaded = torch.from_numpy(_loaded_feature_rows(all_list, self.feature_dict, self.feature_path))
+            picks = eng.kcenter_fused(feats, loaded, self.loaded_feature_weight, labeled_size, select_num, self.metric,
+                                      self.coreset_criteria)
+        else:
+            picks = eng.kcenter(feats, labeled_size, select_num, self.metric, criteria=self.coreset_criteria)
         return [all_list[i] for i in picks.tolist()]
 
 

@@ -18,6 +18,7 @@
 #include "conv_fold.cuh"
 #include "conv_tc.cuh"
 #include "kcenter.cuh"
+#include "kcenter_fused.cuh"
 #include "kmeanpp.cuh"
 #include "prep.cuh"
 #include "topk.cuh"
@@ -1094,6 +1095,70 @@ extern "C" int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, i
   }
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
+extern "C" int b200al_kcenter_fused(b200al_ctx* ctx, const float* d_emb, int D1, const float* d_loaded, int D2, int n,
+                                    int n_init, int metric, int criteria, float loaded_weight, float emb_weight,
+                                    int budget, int64_t* d_picks, float* d_pick_vals, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (budget == 0) return B200AL_OK;
+  if (!d_emb || !d_loaded || !d_picks || n < 1 || budget < 0 || D1 < 1 || D2 < 1 || D1 > 1024)
+    return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (n_init < 1 || n_init > n) return set_err(ctx, B200AL_ERR_ARG, "k-center needs 1 <= n_init <= n initial centres");
+  if (metric != B200AL_L2 && metric != B200AL_COSINE) return set_err(ctx, B200AL_ERR_ARG, "bad metric");
+  if (criteria != B200AL_MIN && criteria != B200AL_MEAN) return set_err(ctx, B200AL_ERR_ARG, "bad criteria");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  int sblocks = (n + 7) / 8;
+  if (sblocks > ctx->sm_count * 8) sblocks = ctx->sm_count * 8;
+  const int nwarps = sblocks * 8;
+  // scratch: state [n] doubles | partial [nwarps] doubles | sums [2] floats | taken [n] | normalised copies (cosine)
+  const size_t norm_elems = metric == B200AL_COSINE ? (size_t)n * (D1 + D2) : 0;
+  const size_t bytes = (size_t)n * 8 + (size_t)nwarps * 8 + 16 + (((size_t)n + 15) & ~(size_t)15) + norm_elems * 4;
+  char* scratch = nullptr;
+  CUDA_TRY(ctx, cudaMalloc(&scratch, bytes));
+  void* state = scratch;
+  double* partial = (double*)(scratch + (size_t)n * 8);
+  float* sums = (float*)(partial + nwarps);
+  uint8_t* taken = (uint8_t*)(sums + 4);
+  float* n1 = (float*)(taken + (((size_t)n + 15) & ~(size_t)15));
+  float* n2 = n1 + (size_t)n * D1;
+  FusedFeats f;
+  f.e1 = d_emb; f.e2 = d_loaded; f.d1 = D1; f.d2 = D2; f.metric = metric;
+  f.s1 = f.s2 = 1.f;
+  f.w2 = loaded_weight;
+  f.w1 = emb_weight;
+  if (metric == B200AL_COSINE) {
+    normalize_rows_kernel<<<(n + 7) / 8, 256, 0, st>>>(d_emb, n1, n, D1);
+    normalize_rows_kernel<<<(n + 7) / 8, 256, 0, st>>>(d_loaded, n2, n, D2);
+    f.e1 = n1; f.e2 = n2;
+    ctx->launches += 2;
+  }
+  // the two global sums (coreset_selector.py:145,153): sums[0] = model embeddings, sums[1] = loaded features
+  pair_distance_sum_kernel<<<sblocks, 256, 0, st>>>(f.e1, n, D1, metric, partial);
+  sum_partials_kernel<<<1, 32, 0, st>>>(partial, nwarps, sums);
+  pair_distance_sum_kernel<<<sblocks, 256, 0, st>>>(f.e2, n, D2, metric, partial);
+  sum_partials_kernel<<<1, 32, 0, st>>>(partial, nwarps, sums + 1);
+  cudaMemsetAsync(taken, 0, n, st);
+  cudaMemsetAsync(taken, 1, n_init, st);
+  kcenter_fused_init_kernel<<<sblocks, 256, 0, st>>>(f, sums, n, n_init, criteria, state);
+  ctx->launches += 5;
+  int blocks = (n + 63) / 64;
+  if (blocks > ctx->kc_blocks) blocks = ctx->kc_blocks;
+  if (blocks < 1) blocks = 1;
+  for (int step = 0; step < budget; ++step) {
+    const double inv = 1.0 / (double)(n_init + step);
+    kcenter_fused_step_kernel<<<blocks, 256, 0, st>>>(f, sums, n, (const long long*)d_picks, step, criteria, state, inv,
+                                                     taken, ctx->kc_part_val, ctx->kc_part_idx);
+    kcenter_pick_kernel<<<1, 256, 0, st>>>(ctx->kc_part_val, ctx->kc_part_idx, blocks, f.e1, D1, taken, ctx->kc_centre,
+                                          (long long*)d_picks, d_pick_vals, step);
+    ctx->launches += 2;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+  cudaFree(scratch);
+  if (e != cudaSuccess) return set_err(ctx, B200AL_ERR_CUDA, "kcenter_fused: %s", cudaGetErrorString(e));
   return B200AL_OK;
 }
 

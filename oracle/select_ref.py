@@ -264,3 +264,50 @@ def hybrid_select(scores: np.ndarray, feats_labeled: np.ndarray, feats_pool: np.
     feats = np.concatenate([feats_labeled, feats_pool[keep_sorted]], 0)
     picks = kcenter_greedy_stream(feats, feats_labeled.shape[0], budget, "l2")
     return [int(keep_sorted[q - feats_labeled.shape[0]]) for q in picks]
+
+
+# ---------------------------------------------------------------------------
+# coreset with externally loaded features, coreset_fusion="add" (coreset_selector.py:110-157)
+# ---------------------------------------------------------------------------
+def pair_distance_sum(feats: np.ndarray, metric: str = "l2") -> float:
+    """`pairwise_distances(feats, metric).sum()` (coreset_selector.py:144-145,152-153) accumulated in fp64 row by row
+    (the reference sums an fp32 matrix with numpy's pairwise fp32 summation: equal to ~1e-6 relative)."""
+    feats = np.ascontiguousarray(feats, dtype=np.float32)
+    fn, f = (l2_rows, feats) if metric == "l2" else (cosine_rows, normalize_rows(feats))
+    return float(sum(fn(f, f[j], j).astype(np.float64).sum() for j in range(f.shape[0])))
+
+
+def kcenter_fused_add_stream(feats: np.ndarray, loaded: np.ndarray, weight: float, n_init: int, budget: int,
+                             metric: str = "l2", criteria: str = "min", return_gaps: bool = False):
+    """k-center greedy on `final = w * D_loaded / sum(D_loaded) + (1 - w) * D_feat / sum(D_feat)`
+    (coreset_selector.py:138-157, fp32 element arithmetic in the reference's order) without building the matrices:
+    running min (fp32) or running sum (fp64) of the fused distance to the growing centre set."""
+    feats = np.ascontiguousarray(feats, dtype=np.float32)
+    loaded = np.ascontiguousarray(loaded, dtype=np.float32)
+    n = feats.shape[0]
+    fn, f, g = (l2_rows, feats, loaded) if metric == "l2" else (cosine_rows, normalize_rows(feats), normalize_rows(loaded))
+    s_feat = np.float32(pair_distance_sum(feats, metric))
+    s_load = np.float32(pair_distance_sum(loaded, metric))
+    w_l, w_f = np.float32(weight), np.float32(1 - weight)
+
+    def fused(j):
+        return (w_l * (fn(g, g[j], j) / s_load) + w_f * (fn(f, f[j], j) / s_feat)).astype(np.float32)
+
+    state = np.zeros(n, np.float64) if criteria == "mean" else np.full(n, np.inf, np.float32)
+    for j in range(n_init):
+        state = state + fused(j) if criteria == "mean" else np.minimum(state, fused(j))
+    taken = np.zeros(n, dtype=bool)
+    taken[:n_init] = True
+    picks, gaps = [], []
+    for step in range(budget):
+        val = (state / float(n_init + step)).astype(np.float32) if criteria == "mean" else state
+        cand = np.where(taken, -np.inf, val)
+        q = int(cand.argmax())
+        if return_gaps:
+            top = cand[q]
+            cand[q] = -np.inf
+            gaps.append(float((top - cand.max()) / top) if n - taken.sum() > 1 else float("inf"))
+        taken[q] = True
+        picks.append(q)
+        state = state + fused(q) if criteria == "mean" else np.minimum(state, fused(q))
+    return (picks, gaps) if return_gaps else picks

@@ -290,3 +290,49 @@ def test_generic_dataloader_path_equals_resident_path(env):
     ad = MirrorActive(MirrorExtendable(base, names[:e["L"]]), MirrorExtendable(base, names[e["L"]:]))
     sel = b200al.B200EntropySelector(batch_size=8, num_workers=0, pin_memory=False, chunk_samples=32)
     assert sel.select_next_batch(ad, e["k"], e["model"], torch.device(DEV)) == e["g"]["selected/entropy"].tolist()
+
+
+def test_kcenter_fused_add_matches_oracle_and_reference_golden(golden):
+    """CoresetSelector with loaded features, coreset_fusion="add" (coreset_selector.py:110-157): the two-matrix
+    k-center kernels (global pair-distance sums + fused running min / sum) vs the streaming oracle on random
+    matrices, and the drop-in selector end to end vs the reference's frozen selections (incl. the cold-start
+    k-means++ branch over the loaded features)."""
+    import os
+    import b200al
+    from oracle import select_ref as S
+    from oracle.make_golden_fused import BUDGET, N_LAB, N_POOL, WEIGHT, loaded_features
+    from oracle.synth import case_name, make_active, synth_pool_u8
+    from oracle.unet_ref import OracleUNet, golden_state_dict
+    rng = np.random.default_rng(21)
+    eng = b200al.Engine(DEV, 2, max_samples=1)
+    try:
+        for n, d2, L, w in ((150, 200, 10, 0.3), (400, 96, 3, 0.8), (64, 1024, 20, 0.5)):
+            feats = (rng.standard_normal((n, 512)) * 0.3 + rng.standard_normal((1, 512))).astype(np.float32)
+            loaded = (rng.standard_normal((n, d2)) + rng.standard_normal((6, d2))[rng.integers(0, 6, n)]).astype(np.float32)
+            for metric in ("l2", "cosine"):
+                for crit in ("min", "mean"):
+                    want, gaps = S.kcenter_fused_add_stream(feats, loaded, w, L, 12, metric, crit, return_gaps=True)
+                    got = eng.kcenter_fused(torch.from_numpy(feats), torch.from_numpy(loaded), w, L, 12, metric, crit)
+                    got = got.cpu().tolist()
+                    if min(gaps) > 1e-5:  # cosine dot products come from an fp32 BLAS GEMM in the oracle
+                        assert got == want, (n, d2, metric, crit, min(gaps))
+                    assert len(set(got)) == 12 and min(got) >= L
+    finally:
+        eng.close()
+    gf = np.load(os.path.join(os.path.dirname(__file__), "golden", "coreset_fused.npz"))
+    names = [case_name(i) for i in range(N_LAB + N_POOL)]
+    fd = loaded_features(names)
+    model = OracleUNet(golden_state_dict(3, golden["model"]))
+    images = synth_pool_u8(N_LAB + N_POOL)
+    kw = dict(batch_size=8, num_workers=0, pin_memory=False, feature_dict=fd, loaded_feature_weight=WEIGHT)
+    for metric in ("l2", "cosine"):
+        for crit in ("min", "mean"):
+            sel = b200al.B200CoresetSelector(metric=metric, coreset_criteria=crit, coreset_fusion="add", **kw)
+            got = sel.select_next_batch(make_active(images, N_LAB), BUDGET, model, torch.device(DEV))
+            assert sorted(got) == gf[f"selected/{metric}/{crit}"].tolist(), (metric, crit)
+    np.random.seed(int(gf["seed/cold"]))
+    cold = b200al.B200CoresetSelector(metric="l2", **kw).select_next_batch(make_active(images, 0), BUDGET, model,
+                                                                          torch.device(DEV))
+    assert cold == gf["selected/cold"].tolist()
+    with pytest.raises(NotImplementedError):
+        b200al.B200CoresetSelector(batch_size=1, num_workers=0, feature_dict=fd, coreset_fusion="cat")

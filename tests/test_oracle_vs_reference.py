@@ -239,3 +239,34 @@ def test_badge_oracle_bit_identical_to_reference_cal_scores(ref, golden):
                                pin_memory=False)
         _names, emb = sel.cal_scores(make_active(images, 2, reference=ref), model, torch.device("cpu"))
         assert np.array_equal(emb, grad_embedding_autograd(sd, images[2:].float().div(255).unsqueeze(1), 1e-5, do_bg))
+
+
+def test_fused_coreset_oracle_matches_reference_live(ref, golden, tmp_path, monkeypatch):
+    """Unmodified reference CoresetSelector with loaded features (coreset_fusion="add") vs the streaming oracle, on a
+    pool / weight / seed different from the frozen golden.  h5py is absent from this image: the reference module's
+    `h5py` attribute is pointed at oracle.make_golden_fused.H5Shim (File + Dataset over numpy files) for the read."""
+    import importlib
+    from oracle import select_ref as S
+    from oracle.make_golden_fused import H5Shim, write_feature_files
+    from oracle.ref_import import build_reference_unet
+    from oracle.synth import make_active, synth_pool_u8
+    from oracle.unet_ref import golden_state_dict
+    cs = importlib.import_module("activelearning.coreset_selector")
+    monkeypatch.setattr(cs, "h5py", H5Shim)
+    sd = golden_state_dict(3, golden["model"])
+    model = build_reference_unet(3)
+    model.load_state_dict(sd)
+    images = synth_pool_u8(5 + 25, start=400)
+    ad = make_active(images, 5, reference=ref)
+    names = list(ad.get_train_dataset().image_idx) + list(ad.get_pool_dataset().image_idx)
+    rng = np.random.default_rng(17)
+    feats = {n: rng.standard_normal(96).astype(np.float32) + (i % 3) for i, n in enumerate(names)}
+    write_feature_files(str(tmp_path), feats)
+    loaded = np.stack([feats[n] for n in names])
+    emb = S.pool_embeddings(sd, images)
+    for metric, crit, w in (("l2", "min", 0.7), ("cosine", "mean", 0.25)):
+        sel = ref.CoresetSelector(batch_size=8, num_workers=0, pin_memory=False, metric=metric, coreset_criteria=crit,
+                                  coreset_fusion="add", feature_path=str(tmp_path), loaded_feature_weight=w)
+        want = sel.select_next_batch(make_active(images, 5, reference=ref), 6, model, torch.device("cpu"))
+        picks = S.kcenter_fused_add_stream(emb, loaded, w, 5, 6, metric, crit)
+        assert sorted(map(str, want)) == sorted(names[i] for i in picks)
