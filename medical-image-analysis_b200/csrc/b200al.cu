@@ -64,6 +64,7 @@ struct Layer {
   CUtensorMap tmA, tmB, tmO;
   ConvTcParams p;
   bool pair = false;   // CTA pairs running M=256 cta_group::2 MMAs (conv_tc.cuh, template PAIR)
+  int mt = 1;          // 2: super-tiles of two pixel tiles sharing one weight tile per CTA (conv_tc.cuh, template MT)
   bool fold = false;   // column-folded kernel (conv_fold.cuh): stride-1 3x3, Cout = 32, Cin in {32, 64}
   ConvFoldParams fp;
   int slots = 0;
@@ -244,7 +245,17 @@ ConvKernelFn pick_cw(int nsplit, int cw) {
   }
   return cw == 32 ? pick_split<BN, BK, 32>(nsplit) : nullptr;
 }
-ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw, bool pair = false) {
+ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw, bool pair = false, int mt = 1) {
+  if (mt == 2) {  // CW = 32, two epilogue groups
+    if (pair || cw != 32) return nullptr;
+#define MT2_KERNEL(BN_, BK_) \
+  (nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<BN_, BK_, 3, 32, false, 2> : (ConvKernelFn)conv_tc_kernel<BN_, BK_, 1, 32, false, 2>)
+    if (bn == 64 && bk == 64) return MT2_KERNEL(64, 64);
+    if (bn == 64 && bk == 32) return MT2_KERNEL(64, 32);
+    if (bn == 128 && bk == 32) return MT2_KERNEL(128, 32);
+#undef MT2_KERNEL
+    return nullptr;
+  }
   if (pair) {  // BK = 64, CW = 32 only
     if (bk != 64 || cw != 32) return nullptr;
     if (bn == 128) return nsplit == 3 ? (ConvKernelFn)conv_tc_kernel<128, 64, 3, 32, true> : (ConvKernelFn)conv_tc_kernel<128, 64, 1, 32, true>;
@@ -265,12 +276,12 @@ ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw, bool pair = false) 
   return nullptr;
 }
 // pair: each CTA of the pair holds half of the weight tile's rows
-int stage_bytes(int bn, int bk, int nsplit, bool pair = false) {
-  return (nsplit == 3 ? 2 : 1) * (128 * bk * 2 + (pair ? bn / 2 : bn) * bk * 2);
+int stage_bytes(int bn, int bk, int nsplit, bool pair = false, int mt = 1) {
+  return (nsplit == 3 ? 2 : 1) * (mt * 128 * bk * 2 + (pair ? bn / 2 : bn) * bk * 2);
 }
 int out_buf_bytes(int cw, int nsplit) { return (nsplit == 3 ? 2 : 1) * 128 * cw * 2; }
-int conv_smem_bytes(int bn, int bk, int nsplit, int stages, int cw, int nbufs_total, bool pair = false) {
-  return stages * stage_bytes(bn, bk, nsplit, pair) + nbufs_total * out_buf_bytes(cw, nsplit) + 1024 + 8 * bn * 4;
+int conv_smem_bytes(int bn, int bk, int nsplit, int stages, int cw, int nbufs_total, bool pair = false, int mt = 1) {
+  return stages * stage_bytes(bn, bk, nsplit, pair, mt) + nbufs_total * out_buf_bytes(cw, nsplit) + 1024 + 8 * bn * 4;
 }
 
 typedef void (*FoldKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const ConvFoldParams, const int);
@@ -355,6 +366,26 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   if (st > 8) st = 8;
   if (st < 2) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "conv tile does not fit shared memory");
   L.stages = st;
+  // Super-tiles (template MT = 2): the N <= 128 layers are bound by the L2->SM operand stream; two pixel tiles per
+  // CTA share every weight tile, one CTA per SM with all of its shared memory.
+  L.mt = 1;
+  // Same-box A/B of bench.py (3 alternations): 1542 -> 1580 images/s (+2.5 %) with SM clocks 1477 -> 1458 MHz under
+  // the power cap; per layer: stride-2 32->64 -20 %, 128->64 at 128^2 -8 %, 128->128 at 64^2 -9 %.
+  // B200AL_MT2: bit 0 = the BN = 64 layers, bit 1 = the BN = 128 layers (BK = 32 there), 0 = off.
+  const int mt2 = env_int("B200AL_MT2", 3);
+  // (not for Cin >= 256: those k-loops are long enough to be MMA-bound already and lose with the smaller BK)
+  if (mt2 && L.kind == KIND_CONV3 && !L.pair && L.cin <= 128 && L.bn >= 64 && L.bn <= 128 &&
+      (mt2 & (L.bn == 64 ? 1 : 2))) {
+    int bk2 = L.bk;
+    if (L.bn == 128) bk2 = 32;  // 2 x 128 x 64-channel tiles + a 128-row weight tile leave room for one stage only
+    if (L.bn == 64 && env_int("B200AL_MT2_BK", 64) == 32) bk2 = 32;
+    const int sb2 = stage_bytes(L.bn, bk2, ctx->nsplit, false, 2);
+    const int st2 = (kMaxSmem - fixed - 2 * out_buf_bytes(32, ctx->nsplit)) / sb2;
+    if (st2 >= 2 && pick_kernel(L.bn, bk2, ctx->nsplit, 32, false, 2)) {
+      L.mt = 2; L.bk = bk2; L.cw = 32; L.ngroups = 2; L.nbuf = 1;
+      L.stages = st2 > 8 ? 8 : st2;
+    }
+  }
   p.taps = L.kind == KIND_CONV3 ? 9 : 1;
   p.chunks = L.cin / L.bk;
   p.n_total = n_total;
@@ -469,7 +500,7 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
     CUDA_TRY(ctx, cudaGetLastError());
     return 0;
   }
-  ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw, L.pair);
+  ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw, L.pair, L.mt);
   if (!fn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no conv kernel for BN=%d BK=%d", L.bn, L.bk);
   ConvTcParams q = p;
   q.n_tiles = p.n_total / L.bn;
@@ -477,11 +508,14 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
   const int resident = ctx->sm_count * L.ctas_per_sm;
   // CTA pairs with multicast weight tiles: pixel tiles come in pairs, one CTA per SM
   const int m_tiles = S * p.tiles_x * p.tiles_y;
-  if (L.pair && m_tiles % 2) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "odd number of pixel tiles in a paired layer");
+  if ((L.pair || L.mt == 2) && m_tiles % 2)
+    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "odd number of pixel tiles in a paired layer");
   q.cluster = L.pair ? 1 : 0;
-  unsigned nblk = (unsigned)(q.total_tiles < resident ? q.total_tiles : resident);
+  q.mt = L.mt;
+  const int work = L.mt == 2 ? q.total_tiles / 2 : q.total_tiles;
+  unsigned nblk = (unsigned)(work < resident ? work : resident);
   if (q.cluster) nblk &= ~1u;
-  const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups, L.pair);
+  const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups, L.pair, L.mt);
   const bool t = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
   if (t) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
   {
@@ -632,19 +666,19 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
     // rows: conv [2 planes][9 taps][Cout]; convT [2 planes][1][4*Cout]
     // (boxes of BN/2 rows: a weight tile is fetched as two halves, see conv_tc.cuh)
     TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn / 2));
-    ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw, L.pair);
+    ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw, L.pair, L.mt);
     if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d CW=%d", L.bn, L.bk, L.cw); b200al_ctx_destroy(ctx); return rc; }
-    const int smem_l = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups, L.pair);
+    const int smem_l = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups, L.pair, L.mt);
     TRY_CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
     int occ = 0;
     TRY_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kConvThreads, smem_l));
-    const int tmem_limit = 512 / (2 * L.bn);  // two accumulator stages per CTA
+    const int tmem_limit = 512 / (2 * L.mt * L.bn);  // two accumulator stages per CTA
     L.ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
     if (L.ctas_per_sm > 2) L.ctas_per_sm = 2;
-    if (L.pair) L.ctas_per_sm = 1;
+    if (L.pair || L.mt == 2) L.ctas_per_sm = 1;
     if (env_int("B200AL_VERBOSE", 0))
-      fprintf(stderr, "b200al plan: kind=%d %d->%d s%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d pair=%d\n", L.kind,
-              L.cin, L.cout, L.stride, L.bn, L.bk, L.stages, L.cw, L.nbuf, L.ngroups, smem_l, L.ctas_per_sm, (int)L.pair);
+      fprintf(stderr, "b200al plan: kind=%d %d->%d s%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d pair=%d mt=%d\n", L.kind,
+              L.cin, L.cout, L.stride, L.bn, L.bk, L.stages, L.cw, L.nbuf, L.ngroups, smem_l, L.ctas_per_sm, (int)L.pair, L.mt);
   }
   TRY_RC(dev_alloc(ctx, &ctx->first_w, 32 * 9));
   TRY_RC(dev_alloc(ctx, &ctx->first_bias, 32));

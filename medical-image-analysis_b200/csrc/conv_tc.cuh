@@ -54,17 +54,20 @@ struct ConvTcParams {
   // 1: launched as clusters of 2 CTAs (template PAIR) that run one M=256 cta_group::2 MMA over two adjacent
   // pixel tiles of the same n-tile; each CTA loads its own pixel tile and HALF of the weight tile
   int cluster;
+  // 2: every CTA walks SUPER-tiles of two adjacent pixel tiles that share one weight tile in shared memory
+  // (template MT == 2): the weight bytes per MMA halve without any cross-CTA traffic.  1 otherwise.
+  int mt;
 };
 
 constexpr int kConvThreads = 320;  // TMA warp + MMA warp + 2 epilogue groups of 4 warps
 
 // smem: [stages x (A planes, B planes)] [nbuf x planes x 128 x CW staging for the TMA store] [barriers] [affine]
-template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR = false>
+template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR = false, int MT = 1>
 struct ConvTcSmem {
   static constexpr int kPlanes = (NSPLIT == 3) ? 2 : 1;
   static constexpr int kABytes = 128 * BK * 2;
   static constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * BK * 2;  // rows of B held by this CTA
-  static constexpr int kStageBytes = kPlanes * (kABytes + kBBytes);
+  static constexpr int kStageBytes = kPlanes * (MT * kABytes + kBBytes);  // [A tile(s): hi, lo per tile][B: hi, lo]
   static constexpr int kOutWarpBytes = 32 * CW * 2;                  // one warp's 32 rows of one plane
   static constexpr int kOutBufBytes = kPlanes * 4 * kOutWarpBytes;   // one staging buffer
   static constexpr int kTailBytes = 1024;  // barriers, tmem ptr
@@ -80,6 +83,11 @@ __device__ __forceinline__ bool get_tile(const ConvTcParams& p, int i, int block
   int nt, m;
   if (p.cluster) {
     const int pair = (int)(blockIdx.x >> 1) + i * (int)(gridDim.x >> 1);
+    if (pair >= (p.total_tiles >> 1)) return false;
+    nt = pair % p.n_tiles;
+    m = (pair / p.n_tiles) * 2 + (int)rank;
+  } else if (p.mt == 2) {  // rank = which of the super-tile's two pixel tiles
+    const int pair = (int)blockIdx.x + i * (int)gridDim.x;
     if (pair >= (p.total_tiles >> 1)) return false;
     nt = pair % p.n_tiles;
     m = (pair / p.n_tiles) * 2 + (int)rank;
@@ -99,14 +107,15 @@ __device__ __forceinline__ bool get_tile(const ConvTcParams& p, int i, int block
   return true;
 }
 
-template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR>
+template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR, int MT = 1>
 __global__ void __launch_bounds__(kConvThreads)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const ConvTcParams p, const int stages, const int nbuf, const int ngroups) {
-  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW, PAIR>;
+  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW, PAIR, MT>;
   static_assert(BLOCK_N % CW == 0 && (CW == 32 || CW == 64), "bad store chunk width");
+  static_assert(MT == 1 || (MT == 2 && !PAIR && 4 * BLOCK_N <= 512), "super-tiles: two pixel tiles, one CTA");
   constexpr uint32_t kRowBytes = BK * 2;  // 128 -> SW128, 64 -> SW64
-  constexpr uint32_t kTmemCols = 2 * BLOCK_N;  // two accumulator stages (power of two >= 64)
+  constexpr uint32_t kTmemCols = 2 * MT * BLOCK_N;  // two accumulator stages of MT tiles (power of two >= 64)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the swizzled tiles (checked below; the host adds no slack)
   uint8_t* smem = smem_raw;
@@ -140,7 +149,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(smem_u32(&tfull_bar[i]), 1);
-      mbar_init(smem_u32(&tempty_bar[i]), PAIR ? 8 : 4);  // one arrive per epilogue warp (of both CTAs)
+      mbar_init(smem_u32(&tempty_bar[i]), (PAIR || MT == 2) ? 8 : 4);  // one arrive per epilogue warp that reads it
     }
     fence_barrier_init();
   }
@@ -160,8 +169,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      TileCoord tc;
+      TileCoord tc, tc1;
       for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tc); ++i) {
+        if (MT == 2) get_tile(p, i, BLOCK_N, 1u, &tc1);
         for (int kb = 0; kb < num_kb; ++kb) {
           const int tap = kb / p.chunks;
           const int ch = kb - tap * p.chunks;
@@ -186,9 +196,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             mbar_arrive_expect_tx(fb, L::kStageBytes);
             tma_load_5d(smem_u32(st), &tmA, fb, c, cx, cp, cy, tc.sample);
             if (NSPLIT == 3) tma_load_5d(smem_u32(st + L::kABytes), &tmA, fb, c + p.a_lo_off, cx, cp, cy, tc.sample);
+            if (MT == 2) {  // second pixel tile of the super-tile
+              uint8_t* st1 = st + L::kPlanes * L::kABytes;
+              const int cx1 = tc1.x0 + p.a_dx[s], cy1 = tc1.y0 + p.a_dy[r];
+              tma_load_5d(smem_u32(st1), &tmA, fb, c, cx1, cp, cy1, tc1.sample);
+              if (NSPLIT == 3)
+                tma_load_5d(smem_u32(st1 + L::kABytes), &tmA, fb, c + p.a_lo_off, cx1, cp, cy1, tc1.sample);
+            }
             // the weight tile is fetched as two boxes of BLOCK_N/2 rows per plane (one tensor map serves both modes)
             for (int pl = 0; pl < L::kPlanes; ++pl) {
-              uint8_t* bdst = st + L::kPlanes * L::kABytes + pl * L::kBBytes;
+              uint8_t* bdst = st + MT * L::kPlanes * L::kABytes + pl * L::kBBytes;
               const int row = (pl * p.taps + tap) * p.n_total + tc.n0;
               tma_load_2d(smem_u32(bdst), &tmB, fb, ch * BK, row);
               tma_load_2d(smem_u32(bdst + L::kBBytes / 2), &tmB, fb, ch * BK, row + BLOCK_N / 2);
@@ -213,13 +230,13 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tcm); ++i) {
         mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);  // epilogue(s) have drained this accumulator
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BLOCK_N;
+        const uint32_t d_tmem = tmem_base + acc * (MT * BLOCK_N);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(smem_u32(&full_bar[stage]), phase);
           tc_fence_after();
           const uint32_t a_hi = ring_lo + (uint32_t)stage * (L::kStageBytes >> 4);
           const uint32_t a_lo = a_hi + (L::kABytes >> 4);
-          const uint32_t b_hi = a_hi + ((L::kPlanes * L::kABytes) >> 4);
+          const uint32_t b_hi = a_hi + ((MT * L::kPlanes * L::kABytes) >> 4);
           const uint32_t b_lo = b_hi + (L::kBBytes >> 4);
           if (elect_one()) {
 #pragma unroll
@@ -238,6 +255,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (NSPLIT == 3) {
                   umma_bf16(d_tmem, da, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
                   umma_bf16(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
+                }
+                if (MT == 2) {  // second pixel tile against the same weight tile, its own accumulator
+                  constexpr uint32_t kA1 = (L::kPlanes * L::kABytes) >> 4;
+                  const uint64_t da1 = make_desc(a_hi + kA1 + 2 * k, kDescHi);
+                  umma_bf16(d_tmem + BLOCK_N, da1, db, idesc, accum);
+                  if (NSPLIT == 3) {
+                    umma_bf16(d_tmem + BLOCK_N, da1, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
+                    umma_bf16(d_tmem + BLOCK_N, make_desc(a_lo + kA1 + 2 * k, kDescHi), db, idesc, 1u);
+                  }
                 }
               }
             }
@@ -267,8 +293,11 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     int obuf = 0, ebuf = 0;
     uint8_t* gstaging = staging + (size_t)group * nbuf * L::kOutBufBytes;
     TileCoord tc;
-    for (int it = 0; get_tile(p, it, BLOCK_N, rank, &tc); ++it) {
-      if (group >= ngroups || (ngroups == 2 && (it & 1) != group)) continue;
+    // MT == 2: both groups work on every super-tile, group g drains the accumulator of its g-th pixel tile
+    const uint32_t trank = MT == 2 ? (uint32_t)group : rank;
+    const uint32_t tcol = MT == 2 ? (uint32_t)group * BLOCK_N : 0u;
+    for (int it = 0; get_tile(p, it, BLOCK_N, trank, &tc); ++it) {
+      if (MT == 1 && (group >= ngroups || (ngroups == 2 && (it & 1) != group))) continue;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
       float* esa = es + (group * 2 + ebuf) * BLOCK_N;
       float* eha = eh + (group * 2 + ebuf) * BLOCK_N;
@@ -297,7 +326,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int h = 0; h < CW / 32; ++h) {
           uint32_t v[32];
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * BLOCK_N + c0 + h * 32), v);
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * (MT * BLOCK_N) + c0 + h * 32) + tcol, v);
           tmem_ld_wait();
           if (c0 + CW >= BLOCK_N && h == CW / 32 - 1) {  // last read of this accumulator: hand it back
             tc_fence_before();

@@ -31,14 +31,14 @@ def _engine(K, env=None, **kw):
 
 @pytest.mark.parametrize("K", [2, 3])
 def test_specialised_kernels_equal_generic_path(golden, K):
-    """Folded conv + fused head vs. the generic per-tap kernel + separate head: same operands,
-    different summation order only -> scores agree to 1e-5 relative, logits to 1e-3 absolute."""
+    """Folded conv + fused head + super-tiles + CTA pairs vs. the plain generic per-tap kernel + separate head: same
+    operands, different summation order only -> scores agree to 1e-5 relative, logits to 1e-3 absolute."""
     from oracle.synth import synth_pool_u8
     from oracle.unet_ref import golden_state_dict
     sd = golden_state_dict(K, golden["model"])
     imgs = synth_pool_u8(12, start=500).to(DEV)
     fast = _engine(K, max_samples=8)
-    slow = _engine(K, {"B200AL_FOLD": "0", "B200AL_FUSE_HEAD": "0"}, max_samples=8)
+    slow = _engine(K, {"B200AL_FOLD": "0", "B200AL_FUSE_HEAD": "0", "B200AL_MT2": "0", "B200AL_PAIR": "0"}, max_samples=8)
     try:
         fast.load_model(sd)
         slow.load_model(sd)
