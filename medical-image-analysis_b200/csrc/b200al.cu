@@ -191,6 +191,8 @@ int load_encode_fn(b200al_ctx* ctx) {
   return 0;
 }
 
+int env_int(const char* name, int dflt);
+
 // A operand: activations [S, H, W, pitch] viewed 5-D.  stride 1: (pitch, W, 1, H, S);
 // stride 2: (2*pitch, W/2, 2, H/2, S) so that every filter tap is a dense box.
 int make_tma_act(b200al_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int S, int H, int W, int pitch,
@@ -206,10 +208,20 @@ int make_tma_act(b200al_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, in
   }
   cuuint32_t box[5] = {(cuuint32_t)bk, (cuuint32_t)tw, 1, (cuuint32_t)th, 1};
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  // L2 promotion.  Stride-1 boxes sweep whole pixels, 256 B is free.  Stride-2 boxes skip every other pixel and
+  // the hi and lo planes of one pixel arrive through two different boxes: with a promotion wider than one plane
+  // of a pixel both requests miss and both fetch the promoted block, and ncu shows DRAM reads at exactly 2x the
+  // tensor (profiles/r01_l2promo_stride2.txt: encoder.levels.1.0 1077 -> 537 MB per 64 samples at 64 B,
+  // encoder.levels.2.0 538 -> 269 MB at 128 B).  So: one plane of a pixel, capped at 128 B.
+  int promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
+  if (stride == 2) {
+    promo = pitch <= 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+    promo = env_int("B200AL_L2PROMO_S2", promo);
+  }
   CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<__nv_bfloat16*>(base), dims, strides,
                            box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                            bk == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
-                           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+                           (CUtensorMapL2promotion)promo, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return set_err(ctx, B200AL_ERR_CUDA, "cuTensorMapEncodeTiled(act) failed: %d", (int)r);
   return 0;
 }
