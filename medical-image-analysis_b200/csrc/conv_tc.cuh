@@ -115,7 +115,14 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   static_assert(BLOCK_N % CW == 0 && (CW == 32 || CW == 64), "bad store chunk width");
   static_assert(MT == 1 || (MT == 2 && !PAIR && 4 * BLOCK_N <= 512), "super-tiles: two pixel tiles, one CTA");
   constexpr uint32_t kRowBytes = BK * 2;  // 128 -> SW128, 64 -> SW64
-  constexpr uint32_t kTmemCols = 2 * MT * BLOCK_N;  // two accumulator stages of MT tiles (power of two >= 64)
+  // Stacked B (N <= 64, bf16x3): one tcgen05.mma costs max(math, shared-memory operand read) and the 128-row A
+  // tile alone takes 32 cycles to read, so a 128 x 64 x 16 MMA runs 48 cycles for 32 cycles of math
+  // (tools/mma_bench.cu).  The hi and lo weight tiles are adjacent in shared memory, so a_hi * [w_hi ; w_lo] is ONE
+  // MMA of N = 2 * BLOCK_N into a double-width accumulator (64 cycles, all math) and a_lo * w_hi adds into its
+  // first half: 112 cycles per k-step instead of 144; the epilogue sums the two halves.
+  constexpr bool STACK = NSPLIT == 3 && !PAIR && BLOCK_N <= 64 && 4 * MT * BLOCK_N <= 512;
+  constexpr uint32_t ACCW = STACK ? 2 * BLOCK_N : BLOCK_N;  // TMEM columns of one pixel tile's accumulator
+  constexpr uint32_t kTmemCols = 2 * MT * ACCW;  // two accumulator stages of MT tiles (power of two >= 64)
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-byte alignment for the swizzled tiles (checked below; the host adds no slack)
   uint8_t* smem = smem_raw;
@@ -230,7 +237,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tcm); ++i) {
         mbar_wait(smem_u32(&tempty_bar[acc]), acc_phase ^ 1);  // epilogue(s) have drained this accumulator
         tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * (MT * BLOCK_N);
+        const uint32_t d_tmem = tmem_base + acc * (MT * ACCW);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(smem_u32(&full_bar[stage]), phase);
           tc_fence_after();
@@ -249,6 +256,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 if (NSPLIT == 3) {
                   umma_bf16_pair(d_tmem, da, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
                   umma_bf16_pair(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
+                }
+              } else if (STACK) {
+                constexpr uint32_t idesc2 = umma_idesc_bf16(128, 2 * BLOCK_N);
+                umma_bf16(d_tmem, da, db, idesc2, accum);  // [hi*hi | hi*lo]: B rows run on from w_hi into w_lo
+                umma_bf16(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
+                if (MT == 2) {
+                  constexpr uint32_t kA1 = (L::kPlanes * L::kABytes) >> 4;
+                  umma_bf16(d_tmem + ACCW, make_desc(a_hi + kA1 + 2 * k, kDescHi), db, idesc2, accum);
+                  umma_bf16(d_tmem + ACCW, make_desc(a_lo + kA1 + 2 * k, kDescHi), db, idesc, 1u);
                 }
               } else {
                 umma_bf16(d_tmem, da, db, idesc, accum);
@@ -295,7 +311,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     TileCoord tc;
     // MT == 2: both groups work on every super-tile, group g drains the accumulator of its g-th pixel tile
     const uint32_t trank = MT == 2 ? (uint32_t)group : rank;
-    const uint32_t tcol = MT == 2 ? (uint32_t)group * BLOCK_N : 0u;
+    const uint32_t tcol = MT == 2 ? (uint32_t)group * ACCW : 0u;
     for (int it = 0; get_tile(p, it, BLOCK_N, trank, &tc); ++it) {
       if (MT == 1 && (group >= ngroups || (ngroups == 2 && (it & 1) != group))) continue;
       const uint32_t acc = it & 1, acc_phase = (it >> 1) & 1;
@@ -326,8 +342,17 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 #pragma unroll
         for (int h = 0; h < CW / 32; ++h) {
           uint32_t v[32];
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * (MT * BLOCK_N) + c0 + h * 32) + tcol, v);
-          tmem_ld_wait();
+          const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(acc * (MT * ACCW) + c0 + h * 32) + tcol;
+          tmem_ld_32x32(taddr, v);
+          if (STACK) {  // second half of the stacked accumulator: the hi*lo products
+            uint32_t w[32];
+            tmem_ld_32x32(taddr + BLOCK_N, w);
+            tmem_ld_wait();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) v[j] = __float_as_uint(__uint_as_float(v[j]) + __uint_as_float(w[j]));
+          } else {
+            tmem_ld_wait();
+          }
           if (c0 + CW >= BLOCK_N && h == CW / 32 - 1) {  // last read of this accumulator: hand it back
             tc_fence_before();
             __syncwarp();
