@@ -53,7 +53,11 @@ struct ConvFoldParams {
 constexpr int kFoldThreads = 320;   // TMA warp, MMA warp, 2 epilogue groups of 4 warps
 constexpr int kFoldN = 96;          // 3 column taps x 32 output channels
 constexpr int kFoldValid = 30;      // output columns per tile
-constexpr int kFoldAccStride = 128; // TMEM columns between the two accumulators
+// TMEM columns between the two accumulators.  Stacked (CIN == 64, bf16x3): a_hi * [w_hi ; w_lo] is ONE MMA of
+// N = 192 into a double-width accumulator (the hi and lo weight blocks of a filter row are adjacent in shared
+// memory; 96 cycles, all math, instead of 2 x 56 shared-memory-read-bound cycles), a_lo * w_hi adds into its first
+// 96 columns and the epilogue sums the halves.
+__host__ __device__ constexpr int fold_acc_stride(bool stack) { return stack ? 256 : 128; }
 
 // Each persistent CTA owns a contiguous range of tiles (sample-major, then tile row, then tile
 // column) and steps through it without divisions.
@@ -106,7 +110,9 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                  const __grid_constant__ CUtensorMap tmO, const ConvFoldParams p, const int slots) {
   using L = ConvFoldSmem<CIN, NSPLIT>;
   constexpr uint32_t kRowBytes = L::kRowBytes;
-  constexpr uint32_t kTmemCols = 256;
+  constexpr bool STACK = !L::kPacked && NSPLIT == 3;
+  constexpr uint32_t kFoldAccStride = fold_acc_stride(STACK);
+  constexpr uint32_t kTmemCols = 2 * kFoldAccStride;
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* wsm = smem_raw;
   uint8_t* ring = wsm + L::kWBytes;
@@ -171,7 +177,7 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int pl = 0; pl < L::kPlanes; ++pl)
           for (int r = 0; r < 3; ++r)
             for (int s3 = 0; s3 < 3; ++s3)  // 32 of the layer's output channels per column tap
-              tma_load_2d(smem_u32(wsm + (pl * 3 + r) * L::kWBlockBytes + s3 * 32 * kRowBytes), &tmW, wb, 0,
+              tma_load_2d(smem_u32(wsm + (r * L::kPlanes + pl) * L::kWBlockBytes + s3 * 32 * kRowBytes), &tmW, wb, 0,
                           (pl * 9 + r * 3 + s3) * p.w_cout_total + p.w_co0);
       }
       int slot = 0;
@@ -200,6 +206,7 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // walks the loop (descriptor arithmetic stays on the uniform datapath), an elected lane issues,
     // and the NEXT tile's barriers are polled and its descriptors built half-way through this tile.
     constexpr uint32_t idesc = umma_idesc_bf16(128, kFoldN);
+    constexpr uint32_t idesc2 = umma_idesc_bf16(128, 2 * kFoldN);
     constexpr uint32_t kDescHi = umma_smem_desc_hi(kRowBytes);
     constexpr int KS = L::kPacked ? 2 : CIN / 16;   // k16 steps per filter row and plane
     constexpr int NA = 3 * KS;                      // A descriptors per plane
@@ -213,9 +220,10 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     for (int r = 0; r < 3; ++r)
 #pragma unroll
       for (int k = 0; k < KS; ++k) {
-        const uint32_t wo = w_base + ((r * L::kWBlockBytes + k * 32) >> 4);
+        // packed: [r][96 rows of hi 64 B | lo 64 B]; otherwise [r][plane][96 rows]
+        const uint32_t wo = w_base + (((L::kPacked ? r : r * L::kPlanes) * L::kWBlockBytes + k * 32) >> 4);
         dwh[r * KS + k] = make_desc(wo, kDescHi);
-        dwl[r * KS + k] = make_desc(wo + (L::kPacked ? 4u : (uint32_t)((3 * L::kWBlockBytes) >> 4)), kDescHi);
+        dwl[r * KS + k] = make_desc(wo + (L::kPacked ? 4u : (uint32_t)(L::kWBlockBytes >> 4)), kDescHi);
       }
     const int n_my = (int)((long long)p.total_tiles * (blockIdx.x + 1) / gridDim.x) -
                      (int)((long long)p.total_tiles * blockIdx.x / gridDim.x);
@@ -297,8 +305,12 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (mma_on && elect_one()) {
 #pragma unroll
           for (int m = 0; m < NA / 2; ++m) {
-            umma_bf16(d_tmem, dah[m], dwh[m], idesc, m > 0 ? 1u : 0u);
-            if (NSPLIT == 3) umma_bf16(d_tmem, dah[m], dwl[m], idesc, 1u);
+            if (STACK) {
+              umma_bf16(d_tmem, dah[m], dwh[m], idesc2, m > 0 ? 1u : 0u);  // [hi*hi | hi*lo]
+            } else {
+              umma_bf16(d_tmem, dah[m], dwh[m], idesc, m > 0 ? 1u : 0u);
+              if (NSPLIT == 3) umma_bf16(d_tmem, dah[m], dwl[m], idesc, 1u);
+            }
           }
         }
         // second slot of this tile (lo plane) or, in bf16 mode, the next tile's slot
@@ -317,8 +329,12 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (mma_on) {
 #pragma unroll
             for (int m = NA / 2; m < NA; ++m) {
-              umma_bf16(d_tmem, dah[m], dwh[m], idesc, 1u);
-              if (NSPLIT == 3) umma_bf16(d_tmem, dah[m], dwl[m], idesc, 1u);
+              if (STACK) {
+                umma_bf16(d_tmem, dah[m], dwh[m], idesc2, 1u);
+              } else {
+                umma_bf16(d_tmem, dah[m], dwh[m], idesc, 1u);
+                if (NSPLIT == 3) umma_bf16(d_tmem, dah[m], dwl[m], idesc, 1u);
+              }
             }
           }
           umma_commit(smem_u32(&empty_bar[slot]));
@@ -407,16 +423,37 @@ conv_fold_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int row = lane - 1;  // staging row of this lane's output pixel (lanes 1..30)
       // pull the whole accumulator into registers and hand the TMEM stage back before the math
       uint32_t dd[2][3][16];
+      if (!STACK) {
 #pragma unroll
-      for (int h = 0; h < 2; ++h)
+        for (int h = 0; h < 2; ++h)
 #pragma unroll
-        for (int s3 = 0; s3 < 3; ++s3) tmem_ld_32x32_x16(trow + s3 * 32 + h * 16, dd[h][s3]);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
+          for (int s3 = 0; s3 < 3; ++s3) tmem_ld_32x32_x16(trow + s3 * 32 + h * 16, dd[h][s3]);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
+      }
 #pragma unroll
       for (int h = 0; h < 2; ++h) {  // 16 output channels per pass
+        if (STACK) {  // both halves of the stacked accumulator, 16 channels at a time (register budget)
+          uint32_t e2[3][16];
+#pragma unroll
+          for (int s3 = 0; s3 < 3; ++s3) {
+            tmem_ld_32x32_x16(trow + s3 * 32 + h * 16, dd[h][s3]);
+            tmem_ld_32x32_x16(trow + kFoldN + s3 * 32 + h * 16, e2[s3]);
+          }
+          tmem_ld_wait();
+          if (h == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (elect_one()) mbar_arrive(smem_u32(&tempty_bar[acc]));
+          }
+#pragma unroll
+          for (int s3 = 0; s3 < 3; ++s3)
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              dd[h][s3][j] = __float_as_uint(__uint_as_float(dd[h][s3][j]) + __uint_as_float(e2[s3][j]));
+        }
         const uint32_t(&d0)[16] = dd[h][0];
         const uint32_t(&d1)[16] = dd[h][1];
         const uint32_t(&d2)[16] = dd[h][2];
