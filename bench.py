@@ -174,7 +174,7 @@ def run_reference(args):
 
 def ncu_traffic():
     """DRAM bytes per launch (read + write) from the committed `ncu --set full` summaries of the same kernels at the
-    bench's chunk size (profiles/r01_ncu_full_conv_v9.csv: the conv launches of one 128-sample chunk;
+    bench's chunk size (profiles/r01_ncu_full_conv_v11.csv: the conv launches of one 128-sample chunk;
     profiles/r01_ncu_full_uncertainty_v9.csv: 16 images x T=8 per launch).  None when the files are absent."""
     import csv
     here = os.path.dirname(os.path.abspath(__file__))
@@ -194,7 +194,7 @@ def ncu_traffic():
                 out += float(v) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[unit]
         return out
 
-    conv = [total(r) for r in rows("r01_ncu_full_conv_v9.csv")]
+    conv = [total(r) for r in rows("r01_ncu_full_conv_v11.csv")]
     unc = [total(r) for r in rows("r01_ncu_full_uncertainty_v9.csv")]
     return (sum(conv) / len(conv) if conv else None), (sum(unc) / len(unc) / 16 if unc else None)
 
@@ -337,7 +337,7 @@ def run_b200(args):
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
                          "frac": achieved / tf_peak, "traffic": conv_traffic,
                          "traffic_note": "mean DRAM read+write bytes per conv launch of a 128-sample chunk, ncu --set full "
-                                         "(profiles/r01_ncu_full_conv_v9.csv); tensor-bound kernels, shown for completeness",
+                                         "(profiles/r01_ncu_full_conv_v11.csv); tensor-bound kernels, shown for completeness",
                          "kernel": "conv_fold_kernel + conv_tc_kernel (tcgen05 implicit GEMM, the 21 conv/convT layers)",
                          "launches_timed": int(conv_n), "avg_launch_ms": conv_ms / max(conv_n, 1),
                          "flops_note": "algorithmic 2*MAC of the fp32 reference conv; bf16x3 issues 3 MMAs per product, "

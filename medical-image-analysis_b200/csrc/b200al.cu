@@ -196,7 +196,7 @@ int env_int(const char* name, int dflt);
 // A operand: activations [S, H, W, pitch] viewed 5-D.  stride 1: (pitch, W, 1, H, S);
 // stride 2: (2*pitch, W/2, 2, H/2, S) so that every filter tap is a dense box.
 int make_tma_act(b200al_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, int S, int H, int W, int pitch,
-                 int stride, int bk, int tw, int th) {
+                 int stride, int bk, int tw, int th, int win_ch = 0) {
   cuuint64_t dims[5], strides[4];
   const cuuint64_t pb = (cuuint64_t)pitch * 2;
   if (stride == 1) {
@@ -209,13 +209,15 @@ int make_tma_act(b200al_ctx* ctx, CUtensorMap* tm, const __nv_bfloat16* base, in
   cuuint32_t box[5] = {(cuuint32_t)bk, (cuuint32_t)tw, 1, (cuuint32_t)th, 1};
   cuuint32_t estr[5] = {1, 1, 1, 1, 1};
   // L2 promotion.  Stride-1 boxes sweep whole pixels, 256 B is free.  Stride-2 boxes skip every other pixel and
-  // the hi and lo planes of one pixel arrive through two different boxes: with a promotion wider than one plane
-  // of a pixel both requests miss and both fetch the promoted block, and ncu shows DRAM reads at exactly 2x the
-  // tensor (profiles/r01_l2promo_stride2.txt: encoder.levels.1.0 1077 -> 537 MB per 64 samples at 64 B,
-  // encoder.levels.2.0 538 -> 269 MB at 128 B).  So: one plane of a pixel, capped at 128 B.
+  // the hi and lo planes of one pixel arrive through two different boxes (and in a CAT buffer the other half of
+  // the plane belongs to the decoder): with a promotion wider than the channel window of one plane the requests
+  // fetch bytes nobody reads, and ncu shows DRAM reads at exactly 2x the tensor
+  // (profiles/r01_l2promo_stride2.txt: encoder.levels.1.0 1077 -> 537 MB per 64 samples at 64 B,
+  // encoder.levels.2.0 538 -> 269 MB at 128 B).  So: the window of one plane (win_ch channels), capped at 128 B.
   int promo = CU_TENSOR_MAP_L2_PROMOTION_L2_256B;
   if (stride == 2) {
-    promo = pitch <= 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
+    const int win_bytes = (win_ch > 0 ? win_ch : pitch / 2) * 2;
+    promo = win_bytes <= 64 ? CU_TENSOR_MAP_L2_PROMOTION_L2_64B : CU_TENSOR_MAP_L2_PROMOTION_L2_128B;
     promo = env_int("B200AL_L2PROMO_S2", promo);
   }
   CUresult r = ctx->encode(tm, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<__nv_bfloat16*>(base), dims, strides,
@@ -478,7 +480,7 @@ int make_layer_maps(b200al_ctx* ctx, const Layer& L, const __nv_bfloat16* in, co
     return make_tma_act(ctx, tmO, out, S, outH, outW, 2 * ob.c_total, 1, 32, kFoldValid, 1);
   }
   if ((rc = make_tma_act(ctx, tmA, in, S, inH, inW, 2 * ib.c_total, L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw,
-                         L.p.th)))
+                         L.p.th, L.cin)))
     return rc;
   // output map: box = one epilogue warp's 2 image rows x 16 px x CW channels; transposed conv uses the stride-2 view
   return make_tma_act(ctx, tmO, out, S, outH, outW, 2 * ob.c_total, L.kind == KIND_CONVT ? 2 : 1, L.cw, 16, 2);
