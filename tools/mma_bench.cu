@@ -61,7 +61,7 @@ __global__ void __launch_bounds__(384) mma_loop(int iters, int same_a, long long
 // Tile protocol of the conv kernels: the issuer waits for a free accumulator stage, issues `per_tile`
 // MMAs, commits to tfull[stage]; a consumer warp waits tfull and hands the stage back via tempty.
 template <int N, int ROWB>
-__global__ void __launch_bounds__(128) mma_tiles(int tiles, int per_tile, int nstages, long long* out_cycles) {
+__global__ void __launch_bounds__(128) mma_tiles(int tiles, int per_tile, int nstages, long long* out_cycles, int mode = 0) {
   extern __shared__ __align__(1024) uint8_t smem[];
   __shared__ uint64_t tfull[4], tempty[4];
   __shared__ uint32_t tmem_slot;
@@ -85,14 +85,17 @@ __global__ void __launch_bounds__(128) mma_tiles(int tiles, int per_tile, int ns
     long long t0 = clock64();
     int st = 0; uint32_t ph = 0;
     for (int t = 0; t < tiles; ++t) {
-      mbar_wait(smem_u32(&tempty[st]), ph ^ 1);
-      tc_fence_after();
+      // mode bits (where does the per-tile bubble come from?): 1 = always accumulate, 2 = one accumulator address,
+      // 4 = no tempty wait, 8 = no fence, 16 = no commit (one at the very end)
+      if (!(mode & 4)) mbar_wait(smem_u32(&tempty[st]), ph ^ 1);
+      if (!(mode & 8)) tc_fence_after();
       if (elect_one()) {
+        const uint32_t d = tmem + ((mode & 2) ? 0 : st * 128);
         for (int k = 0; k < per_tile; ++k) {
           const uint32_t a = a0 + (k & 3) * ((128 * ROWB) >> 4) + ((k >> 2) & 1) * 2;
-          umma_bf16(tmem + st * 128, make_desc(a, hi), make_desc(b0 + ((k >> 2) & 1) * 2, hi), idesc, k > 0);
+          umma_bf16(d, make_desc(a, hi), make_desc(b0 + ((k >> 2) & 1) * 2, hi), idesc, (mode & 1) ? 1u : (k > 0));
         }
-        umma_commit(smem_u32(&tfull[st]));
+        if (!(mode & 16) || t == tiles - 1) umma_commit(smem_u32(&tfull[st]));
       }
       __syncwarp();
       if (++st == nstages) { st = 0; ph ^= 1; }
@@ -101,7 +104,7 @@ __global__ void __launch_bounds__(128) mma_tiles(int tiles, int per_tile, int ns
     if (threadIdx.x == 32) out_cycles[blockIdx.x] = t1 - t0;
   } else if (warp == 2) {
     int st = 0; uint32_t ph = 0;
-    for (int t = 0; t < tiles; ++t) {
+    for (int t = 0; t < tiles && !(mode & 4); ++t) {
       mbar_wait(smem_u32(&tfull[st]), ph);
       tc_fence_after();
       tc_fence_before();
@@ -278,19 +281,19 @@ void run_kblocks(int per_blk, int variant) {
 }
 
 template <int N, int ROWB>
-void run_tiles(int per_tile, int nstages) {
+void run_tiles(int per_tile, int nstages, int mode = 0) {
   long long* d;
   cudaMalloc(&d, 148 * sizeof(long long));
   const int smem = (4 * 128 + N) * ROWB + 1024;
   cudaFuncSetAttribute(mma_tiles<N, ROWB>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   const int tiles = 1000;
-  for (int rep = 0; rep < 2; ++rep) mma_tiles<N, ROWB><<<148, 128, smem>>>(tiles, per_tile, nstages, d);
+  for (int rep = 0; rep < 2; ++rep) mma_tiles<N, ROWB><<<148, 128, smem>>>(tiles, per_tile, nstages, d, mode);
   cudaError_t e = cudaDeviceSynchronize();
   long long h[148];
   cudaMemcpy(h, d, sizeof(h), cudaMemcpyDeviceToHost);
   double s = 0;
   for (int i = 0; i < 148; ++i) s += h[i];
-  printf("tiles N=%3d per_tile=%2d stages=%d: %.1f cycles/MMA (%s)\n", N, per_tile, nstages,
+  printf("tiles N=%3d per_tile=%2d stages=%d mode=%2d: %.1f cycles/MMA (%s)\n", N, per_tile, nstages, mode,
          s / 148 / ((double)tiles * per_tile), cudaGetErrorString(e));
   cudaFree(d);
 }
@@ -313,7 +316,11 @@ void run(int same_a, int threads = 128) {
   cudaFree(d);
 }
 
-int main() {
+int main(int argc, char** argv) {
+  if (argc > 1) {  // per-tile bubble hunt
+    for (int mode : {0, 1, 2, 3, 4, 8, 12, 20, 28, 31}) run_tiles<96, 128>(18, 2, mode);
+    return 0;
+  }
   for (int v = 7; v < 10; ++v) { run_kblocks<128, 128>(12, v); run_kblocks<64, 128>(12, v); }
   run_kblocks<128, 128>(12, 0); run_kblocks<64, 128>(12, 0);
   run_tiles<96, 128>(18, 2); run_tiles<96, 128>(18, 3); run_tiles<96, 128>(18, 4); run_tiles<96, 128>(36, 2);
