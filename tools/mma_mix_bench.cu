@@ -58,6 +58,62 @@ __global__ void __launch_bounds__(128) mma_loop(int iters, long long* out_cycles
   if (warp == 0) tmem_dealloc(tmem, 256);
 }
 
+// The folded Cin = 64 tile as issued: 12 stacked MMAs (N = 192, D columns 0..191) then 12 of N = 96 into the first half,
+// accumulate = 0 on the first, alternating between two accumulators; no barriers, no commits inside the loop.
+// seq: 0 = as above, 1 = all 24 with N = 192, 2 = all 24 with N = 96, 3 = N alternating every MMA
+__global__ void __launch_bounds__(128) mma_fold_tile(int tiles, int seq, long long* out_cycles) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ uint64_t bar;
+  __shared__ uint32_t tmem_slot;
+  const int warp = threadIdx.x >> 5;
+  constexpr int kABytes = 4 * 128 * 128;
+  for (int i = threadIdx.x; i < (kABytes + 256 * 128) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  if (threadIdx.x == 0) { mbar_init(smem_u32(&bar), 1); fence_barrier_init(); }
+  if (warp == 0) { tmem_alloc(smem_u32(&tmem_slot), 512); tmem_relinquish(); }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = tmem_slot;
+  if (warp == 1) {
+    constexpr uint32_t i192 = umma_idesc_bf16(128, 192), i96 = umma_idesc_bf16(128, 96);
+    constexpr uint32_t hi = umma_smem_desc_hi(128);
+    const uint32_t a0 = umma_smem_desc_lo(smem_u32(smem));
+    const uint32_t b0 = umma_smem_desc_lo(smem_u32(smem + kABytes));
+    long long t0 = clock64();
+    if (elect_one()) {
+      for (int t = 0; t < tiles; ++t) {
+        const uint32_t d = tmem + (t & 1) * 256;
+#pragma unroll
+        for (int m = 0; m < 24; ++m) {
+          const uint32_t a = a0 + (m & 3) * ((128 * 128) >> 4) + ((m >> 2) & 3) * 2;
+          const bool wide = seq == 0 ? m < 12 : (seq == 1 ? true : (seq == 2 ? false : (m & 1) == 0));
+          umma_bf16(d, make_desc(a, hi), make_desc(b0 + ((m >> 2) & 3) * 2, hi), wide ? i192 : i96, m > 0);
+        }
+      }
+      umma_commit(smem_u32(&bar));
+    }
+    __syncwarp();
+    mbar_wait(smem_u32(&bar), 0);
+    long long t1 = clock64();
+    if (threadIdx.x == 32) out_cycles[blockIdx.x] = t1 - t0;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem, 512);
+}
+
+void run_fold_tile(long long* d, int seq) {
+  const int tiles = 500, smem = 4 * 128 * 128 + 256 * 128 + 1024;
+  cudaFuncSetAttribute(mma_fold_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+  for (int rep = 0; rep < 2; ++rep) mma_fold_tile<<<148, 128, smem>>>(tiles, seq, d);
+  long long h = 0;
+  cudaMemcpy(&h, d, sizeof(h), cudaMemcpyDeviceToHost);
+  cudaError_t e = cudaDeviceSynchronize();
+  printf("fold tile seq=%d: %7.1f cycles per tile of 24 MMAs (12 x 96 + 12 x 56 = 1824 expected for seq 0) %s\n", seq,
+         (double)h / tiles, e == cudaSuccess ? "" : cudaGetErrorString(e));
+}
+
 template <int N, int ROWA, int ROWB>
 void run(long long* d) {
   const int iters = 2000, smem = 4 * 128 * ROWA + 256 * ROWB + 1024;
@@ -73,6 +129,7 @@ void run(long long* d) {
 int main() {
   long long* d;
   cudaMalloc(&d, 148 * sizeof(long long));
+  for (int seq = 0; seq < 4; ++seq) run_fold_tile(d, seq);
   run<96, 128, 128>(d);
   run<96, 128, 64>(d);
   run<96, 64, 64>(d);
