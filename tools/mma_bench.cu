@@ -317,6 +317,10 @@ void run(int same_a, int threads = 128) {
 }
 
 int main(int argc, char** argv) {
+  if (argc > 1 && argv[1][0] == 'k') {  // k-block protocol, every issue variant
+    for (int v = 0; v < 10; ++v) { run_kblocks<128, 128>(12, v); run_kblocks<64, 128>(12, v); run_kblocks<96, 128>(6, v); }
+    return 0;
+  }
   if (argc > 1) {  // per-tile bubble hunt
     for (int mode : {0, 1, 2, 3, 4, 8, 12, 20, 28, 31}) run_tiles<96, 128>(18, 2, mode);
     return 0;

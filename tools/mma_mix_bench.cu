@@ -67,7 +67,7 @@ __global__ void __launch_bounds__(128) mma_fold_tile(int tiles, int seq, long lo
   __shared__ uint32_t tmem_slot;
   const int warp = threadIdx.x >> 5;
   constexpr int kABytes = 4 * 128 * 128;
-  for (int i = threadIdx.x; i < (kABytes + 256 * 128) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
+  for (int i = threadIdx.x; i < (kABytes + 6 * 96 * 128) / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
   if (threadIdx.x == 0) { mbar_init(smem_u32(&bar), 1); fence_barrier_init(); }
   if (warp == 0) { tmem_alloc(smem_u32(&tmem_slot), 512); tmem_relinquish(); }
   fence_proxy_async_smem();
@@ -84,6 +84,21 @@ __global__ void __launch_bounds__(128) mma_fold_tile(int tiles, int seq, long lo
     if (elect_one()) {
       for (int t = 0; t < tiles; ++t) {
         const uint32_t d = tmem + (t & 1) * 256;
+        if (seq >= 4) {
+          // the kernel's exact operand walk: A = halo slot (6 x 32 px rows of 128 B), filter row r = +32 rows,
+          // k-slice = +32 B; B = resident weights [r][hi 96 rows | lo 96 rows]; hi slot then lo slot.
+          // seq 5: the same with the k loop outside the r loop (consecutive MMAs touch different rows)
+#pragma unroll
+          for (int ph = 0; ph < 2; ++ph)
+#pragma unroll
+            for (int m = 0; m < 12; ++m) {
+              const int r = seq == 4 ? m / 4 : m % 3, k = seq == 4 ? m % 4 : m / 3;
+              const uint32_t a = a0 + ((ph * 6 * 32 * 128 + r * 32 * 128 + k * 32) >> 4);
+              const uint32_t b = b0 + ((r * 2 * 96 * 128 + k * 32) >> 4);
+              umma_bf16(d, make_desc(a, hi), make_desc(b, hi), ph == 0 ? i192 : i96, (ph | m) > 0);
+            }
+          continue;
+        }
 #pragma unroll
         for (int m = 0; m < 24; ++m) {
           const uint32_t a = a0 + (m & 3) * ((128 * 128) >> 4) + ((m >> 2) & 3) * 2;
@@ -104,7 +119,7 @@ __global__ void __launch_bounds__(128) mma_fold_tile(int tiles, int seq, long lo
 }
 
 void run_fold_tile(long long* d, int seq) {
-  const int tiles = 500, smem = 4 * 128 * 128 + 256 * 128 + 1024;
+  const int tiles = 500, smem = 4 * 128 * 128 + 6 * 96 * 128 + 1024;
   cudaFuncSetAttribute(mma_fold_tile, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
   for (int rep = 0; rep < 2; ++rep) mma_fold_tile<<<148, 128, smem>>>(tiles, seq, d);
   long long h = 0;
@@ -129,7 +144,7 @@ void run(long long* d) {
 int main() {
   long long* d;
   cudaMalloc(&d, 148 * sizeof(long long));
-  for (int seq = 0; seq < 4; ++seq) run_fold_tile(d, seq);
+  for (int seq = 0; seq < 6; ++seq) run_fold_tile(d, seq);
   run<96, 128, 128>(d);
   run<96, 128, 64>(d);
   run<96, 64, 64>(d);
