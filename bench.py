@@ -47,7 +47,8 @@ def parse():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--pool", type=int, default=POOL_PER_GPU, help="images per GPU")
-    ap.add_argument("--chunk", type=int, default=int(os.environ.get("B200AL_CHUNK", 128)), help="samples per forward chunk")
+    ap.add_argument("--chunk", type=int, default=int(os.environ.get("B200AL_CHUNK", 256)),
+                    help="samples per forward chunk (256 = 20 GB of activations; 128 -> 256 is +1.8 %, 512 another +0.4 %)")
     ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16"])
     ap.add_argument("--cpu-sample", type=int, default=12, help="images in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -335,9 +336,12 @@ def run_b200(args):
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
-                         "frac": achieved / tf_peak, "traffic": conv_traffic,
-                         "traffic_note": "mean DRAM read+write bytes per conv launch of a 128-sample chunk, ncu --set full "
-                                         "(profiles/r01_ncu_full_conv_v11.csv); tensor-bound kernels, shown for completeness",
+                         "frac": achieved / tf_peak,
+                         "traffic": conv_traffic * args.chunk / 128 if conv_traffic else None,
+                         "traffic_note": "mean DRAM read+write bytes per conv launch, ncu --set full of a 128-sample chunk "
+                                         "(profiles/r01_ncu_full_conv_v11.csv) scaled to this run's chunk_samples "
+                                         "(traffic is per sample: activations in, activations out); tensor-bound "
+                                         "kernels, shown for completeness",
                          "kernel": "conv_fold_kernel + conv_tc_kernel (tcgen05 implicit GEMM, the 21 conv/convT layers)",
                          "launches_timed": int(conv_n), "avg_launch_ms": conv_ms / max(conv_n, 1),
                          "flops_note": "algorithmic 2*MAC of the fp32 reference conv; bf16x3 issues 3 MMAs per product, "
