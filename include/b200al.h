@@ -39,7 +39,11 @@ enum b200al_status {
 enum b200al_score_mode {    /* which selector's score */
   B200AL_ENTROPY = 0,       /* EntropySelector.cal_scores     entropy_selector.py:45-49 */
   B200AL_MARGIN = 1,        /* MarginSelector.cal_scores      margin_selector.py:45-48 */
-  B200AL_CONFIDENCE = 2     /* ConfidenceSelector.cal_scores  confidence_selector.py:45-47 */
+  B200AL_CONFIDENCE = 2,    /* ConfidenceSelector.cal_scores  confidence_selector.py:45-47 */
+  B200AL_DICE = 3           /* dice-uncertainty (not a reference selector; BASELINE north star):
+                               DiceLoss(pbar, one_hot(argmax pbar)) with the semantics of losses/dice_loss.py:32-72
+                               (do_bg = True, batch = False, squared = False); the `smooth` argument of the scoring
+                               calls is DiceLoss.smooth (1e-5) in this mode */
 };
 enum b200al_metric { B200AL_L2 = 0, B200AL_COSINE = 1 }; /* CoresetSelector(metric=...) */
 enum b200al_criteria { B200AL_MIN = 0, B200AL_MEAN = 1 }; /* CoresetSelector(coreset_criteria=...) */

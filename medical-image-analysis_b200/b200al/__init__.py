@@ -13,6 +13,7 @@ from .selectors import (  # noqa: F401
     B200BADGESelector,
     B200ConfidenceSelector,
     B200CoresetSelector,
+    B200DiceUncertaintySelector,
     B200EntropySelector,
     B200HybridSelector,
     B200KMeanSelector,

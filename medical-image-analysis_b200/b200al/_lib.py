@@ -17,12 +17,12 @@ NUM_UPSAMPLES = 4
 MASK_CHANNELS = 2944
 EMBED_DIM = 512
 
-ENTROPY, MARGIN, CONFIDENCE = 0, 1, 2
+ENTROPY, MARGIN, CONFIDENCE, DICE = 0, 1, 2, 3
 L2, COSINE = 0, 1
 BF16X3, BF16 = 0, 1
 U8, F32 = 0, 1
 
-MODES = {"entropy": ENTROPY, "margin": MARGIN, "confidence": CONFIDENCE}
+MODES = {"entropy": ENTROPY, "margin": MARGIN, "confidence": CONFIDENCE, "dice": DICE}
 METRICS = {"l2": L2, "cosine": COSINE}
 CRIT_MIN, CRIT_MEAN = 0, 1
 CRITERIA = {"min": CRIT_MIN, "mean": CRIT_MEAN}

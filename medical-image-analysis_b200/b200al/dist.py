@@ -88,3 +88,30 @@ def broadcast_state_dict(sd: dict, device, src: int = 0, group=None) -> dict:
         out[k] = flat[off:off + n].view(sd[k].shape)
         off += n
     return out
+
+
+def broadcast_cpu(t: torch.Tensor, src: int = 0, group=None) -> torch.Tensor:
+    """Rank `src`'s copy of a small CPU tensor on every rank (same shape everywhere); identity when not distributed.
+    NCCL groups move it through the current CUDA device."""
+    rank, ws = world()
+    if ws == 1:
+        return t
+    if dist.get_backend(group) == "nccl":
+        d = t.to(torch.device("cuda", torch.cuda.current_device()))
+        dist.broadcast(d, src=src, group=group)
+        return d.cpu()
+    t = t.clone()
+    dist.broadcast(t, src=src, group=group)
+    return t
+
+
+def broadcast_draws(first: int, uniforms, device=None, src: int = 0, group=None):
+    """k-means++ random draws (first centre, uniforms [(k-1), trials] float64 numpy): rank `src`'s values on every
+    rank.  Each rank still consumes its own numpy stream like the single-process reference; only the values agree."""
+    import numpy as np
+    rank, ws = world()
+    if ws == 1:
+        return first, uniforms
+    flat = torch.from_numpy(np.concatenate([[float(first)], np.asarray(uniforms, np.float64).reshape(-1)]))
+    flat = broadcast_cpu(flat, src, group)
+    return int(flat[0].item()), flat[1:].numpy().reshape(np.asarray(uniforms).shape)

@@ -33,6 +33,9 @@ def install_into_al_trainer(trainer_cls, reference_abc=None):
                 kw["coreset_criteria"] = getattr(self.config, "coreset_criteria", "min")
                 kw["sharp_factor"] = getattr(self.config, "kmean_sharp_factor", 1.0)
                 kw["softmax"] = getattr(self.config, "kmean_softmax", False)
+                kw["feature_path"] = getattr(self.config, "feature_path", None)
+                kw["loaded_feature_weight"] = getattr(self.config, "loaded_feature_weight", 1.0)
+                kw["loaded_feature_only"] = getattr(self.config, "loaded_feature_only", False)
             if name == "b200-badge":  # al_trainer.py:871-879
                 kw.update(dice_loss=self.supervised_loss.dice_loss, ce_loss=self.supervised_loss.ce_loss,
                           multiple_loss="add")

@@ -65,7 +65,8 @@ def _cold_start(active_dataset, select_num: int) -> list:
     _, pool_size = active_dataset.get_size()
     scores = torch.rand(pool_size)
     _, indices = torch.sort(scores, descending=True)
-    return [active_dataset.pool_dataset.image_idx[id] for id in indices[:select_num]]
+    indices = D.broadcast_cpu(indices[:select_num])  # multi-GPU: rank 0's draw decides (rank RNG states may differ)
+    return [active_dataset.pool_dataset.image_idx[id] for id in indices]
 
 
 class PoolSource:
@@ -266,6 +267,17 @@ class B200ConfidenceSelector(_B200Uncertainty):
     mode = "confidence"
 
 
+class B200DiceUncertaintySelector(_B200Uncertainty):
+    """Dice-uncertainty (BASELINE.json north star, kernel 3; not a reference selector): score =
+    DiceLoss(p, one_hot(argmax p)) of the (T-averaged) softmax map against its own hard prediction, with the
+    reference's DiceLoss semantics (src/losses/dice_loss.py:32-72: do_bg=True, batch=False, squared=False,
+    smooth 1e-5 as al_trainer.py:785-791 builds it).  `smooth` is DiceLoss.smooth here."""
+    mode = "dice"
+
+    def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-5, **kw):
+        super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
+
+
 class B200MCDropoutEntropySelector(_B200Uncertainty):
     """Entropy of the mean of T MC-dropout softmax maps (not in the reference;
     composed from its UNet + Dropout2d + entropy formula)."""
@@ -283,18 +295,71 @@ def _embed_positions(eng: Engine, src: PoolSource, positions: list[int]) -> torc
     return out
 
 
+KERNEL_WIDTHS = (128, 256, 512, 1024, 1536, 2048)  # row widths the k-center / k-means++ kernels are built for
+
+
+def _pad_to_kernel_width(x: torch.Tensor) -> torch.Tensor:
+    """Zero-pad the columns of x to the next supported width (zero columns change neither l2 nor cosine distances)."""
+    width = next((w for w in KERNEL_WIDTHS if w >= x.shape[1]), None)
+    if width is None:
+        raise NotImplementedError(f"feature rows of dimension {x.shape[1]} (> {KERNEL_WIDTHS[-1]}) are not supported")
+    return torch.nn.functional.pad(x, (0, width - x.shape[1])) if width != x.shape[1] else x
+
+
+def _read_feature_file(feature_path, case) -> "np.ndarray":
+    """The `feature` dataset of `{feature_path}/{case}.h5` (coreset_selector.py:110-119, kmean_selector.py:75-84;
+    needs h5py like the reference), or - where h5py is not installed - `{case}.npy` / `{case}.npz` (key "feature")
+    holding the same array."""
+    import numpy as np
+    from pathlib import Path
+    base = Path(feature_path)
+    h5 = base / f"{case}.h5"
+    if h5.exists():
+        try:
+            import h5py
+        except ImportError as e:
+            raise NotImplementedError(f"{h5} needs h5py (not installed); store the row as {case}.npy / {case}.npz "
+                                      "or pass feature_dict") from e
+        with h5py.File(h5, "r") as f:
+            return np.asarray(f["feature"][:])
+    npy = base / f"{case}.npy"
+    if npy.exists():
+        return np.load(npy)
+    npz = base / f"{case}.npz"
+    if npz.exists():
+        with np.load(npz) as z:
+            return np.asarray(z["feature"])
+    raise FileNotFoundError(f"no feature file for case {case!r} under {base} (.h5 / .npy / .npz)")
+
+
 def _loaded_feature_rows(names, feature_dict=None, feature_path=None):
     """[len(names), D2] float32 array of externally loaded (foundation-model) features: rows of `feature_dict`, or
-    the `feature` dataset of `{feature_path}/{case}.h5` (coreset_selector.py:110-119; needs h5py)."""
+    one file per case under `feature_path` (`_read_feature_file`)."""
     import numpy as np
     if feature_dict is not None:
         return np.stack([np.asarray(feature_dict[n], dtype=np.float32).reshape(-1) for n in names], axis=0)
-    import h5py  # the reference's own dependency
-    rows = []
-    for n in names:
-        with h5py.File(feature_path / f"{n}.h5", "r") as h5f:
-            rows.append(np.asarray(h5f["feature"][:], dtype=np.float32).reshape(-1))
-    return np.stack(rows, axis=0)
+    return np.stack([np.asarray(_read_feature_file(feature_path, n), dtype=np.float32).reshape(-1) for n in names], axis=0)
+
+
+def _cat_scale(d1: int, d2: int, weight: float) -> "np.float32":
+    """`np.sqrt(D1 / D2 * loaded_feature_weight)` (coreset_selector.py:166-170, kmean_selector.py:113-116) as the
+    float32 the reference multiplies with: it pins numpy < 2 (pyproject.toml:21), where `float32_array *
+    np.float64_scalar` stays float32 and the scalar is cast to float32 first (value-based casting)."""
+    import numpy as np
+    return np.float32(np.sqrt(d1 / d2 * weight))
+
+
+def _require_finite(t: torch.Tensor, what: str) -> None:
+    """The selection kernels compare with `>` / `<`, which NaN never satisfies (a diverged model, or a constant row
+    through standardize_rows' division by std = 0): refuse instead of returning an arbitrary selection."""
+    if not bool(torch.isfinite(t).all()):
+        raise RuntimeError(f"non-finite values in the {what}: the selection would be arbitrary")
+
+
+def _check_picks(picks: list, what: str) -> list:
+    if any(i < 0 for i in picks):
+        raise RuntimeError(f"{what}: no selectable row left (non-finite distances?)")
+    return picks
 
 
 class B200CoresetSelector(_B200Base):
@@ -302,9 +367,9 @@ class B200CoresetSelector(_B200Base):
     {min, mean}; model features alone, or fused with externally loaded features by coreset_fusion="add"
     (:138-157: each distance matrix divided by its global sum, mixed with `loaded_feature_weight`).  Loaded features
     come from `feature_path` (`{case}.h5`, needs h5py like the reference) or from `feature_dict` (case name -> row;
-    an extension for callers that already hold them in memory, like KMeanSelector's).  coreset_fusion="cat" with loaded
-    features is not offered: it scales them by a numpy scalar (:170), so the dtype of the whole selection depends on
-    the numpy version."""
+    an extension for callers that already hold them in memory, like KMeanSelector's).  coreset_fusion="cat" (:158-175)
+    concatenates the embeddings with the loaded rows scaled by sqrt(D1 / D2 * loaded_feature_weight) - in float32, the
+    reference's behaviour under its pinned numpy < 2 (`_cat_scale`) - and runs k-center on the joint rows."""
 
     def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8,
                  metric: str = "cosine", coreset_criteria: str = "min", coreset_fusion: str = "add",
@@ -315,13 +380,9 @@ class B200CoresetSelector(_B200Base):
         if coreset_criteria not in ("min", "mean"):
             raise RuntimeError(f"coreset_criteria {coreset_criteria} is undefined")  # coreset_selector.py:38-40
         self.has_loaded = feature_path is not None or feature_dict is not None
-        if self.has_loaded and coreset_fusion != "add":
-            raise NotImplementedError("loaded features are supported with coreset_fusion='add' only")
+        if coreset_fusion not in ("add", "cat"):
+            raise NotImplementedError(f"coreset_fusion {coreset_fusion!r}: only 'add' and 'cat' exist in the reference")
         if feature_path is not None and feature_dict is None:
-            try:
-                import h5py  # noqa: F401
-            except ImportError as e:
-                raise NotImplementedError("feature_path needs h5py (not installed); pass feature_dict instead") from e
             from pathlib import Path
             feature_path = Path(feature_path)
         self.metric = metric
@@ -344,16 +405,15 @@ class B200CoresetSelector(_B200Base):
                 raise ValueError(f"n_samples={pool_size} should be >= n_clusters={select_num}.")
             eng = get_engine(device, 2, 256, 256, self.precision, 1)
             rows = torch.from_numpy(_loaded_feature_rows(pool.image_idx, self.feature_dict, self.feature_path))
-            width = next((w for w in (128, 256, 512, 1024) if w >= rows.shape[1]), None)
-            if width is None:
-                raise NotImplementedError(f"loaded features of dimension {rows.shape[1]} (> 1024) are not supported")
-            X = torch.nn.functional.pad(rows, (0, width - rows.shape[1])).to(eng.device)
+            X = _pad_to_kernel_width(rows).to(eng.device)
+            _require_finite(X, "loaded features")
             rs = np.random.mtrand._rand
             trials = 2 + int(np.log(select_num))
             w = np.ones(pool_size, dtype=np.float32)
             first = int(rs.choice(pool_size, p=w / w.sum()))
             uniforms = np.stack([rs.uniform(size=trials) for _ in range(select_num - 1)]) if select_num > 1 \
                 else np.zeros((0, trials))
+            first, uniforms = D.broadcast_draws(first, uniforms, eng.device)
             picks = eng.kmeans_pp(X, torch.from_numpy(w), first, torch.from_numpy(uniforms), select_num, trials)
             return [pool.image_idx[i] for i in picks.tolist()]
         all_list = list(labeled.image_idx) + list(pool.image_idx)  # labeled rows first (coreset_selector.py:85-88)
@@ -365,28 +425,40 @@ class B200CoresetSelector(_B200Base):
         emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
         emb_p = D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi))))
         feats = torch.cat([emb_l, emb_p], 0)
+        _require_finite(feats, "embeddings")
         if self.has_loaded:
             loaded = torch.from_numpy(_loaded_feature_rows(all_list, self.feature_dict, self.feature_path))
-            picks = eng.kcenter_fused(feats, loaded, self.loaded_feature_weight, labeled_size, select_num, self.metric,
-                                      self.coreset_criteria)
+            _require_finite(loaded, "loaded features")
+            if self.coreset_fusion == "add":
+                picks = eng.kcenter_fused(feats, loaded, self.loaded_feature_weight, labeled_size, select_num,
+                                          self.metric, self.coreset_criteria)
+            else:  # "cat" (:158-175): one distance matrix over [embeddings | scaled loaded rows], no /sum
+                scale = _cat_scale(feats.shape[1], loaded.shape[1], self.loaded_feature_weight)
+                joint = torch.cat([feats, (loaded * torch.tensor(scale)).to(eng.device)], 1)
+                picks = eng.kcenter(_pad_to_kernel_width(joint), labeled_size, select_num, self.metric,
+                                    criteria=self.coreset_criteria)
         else:
             picks = eng.kcenter(feats, labeled_size, select_num, self.metric, criteria=self.coreset_criteria)
-        return [all_list[i] for i in picks.tolist()]
+        return [all_list[i] for i in _check_picks(picks.tolist(), "k-center")]
 
 
 class B200KMeanSelector(_B200Base):
-    """KMeanSelector (src/activelearning/kmean_selector.py:19-196), model features only: row-standardised
-    `get_enc_feature` embeddings (:95-97), sample weight = min / mean distance of each pool row to the labeled rows
-    (:143-145, 174-186) and scikit-learn's weighted k-means++ seeding over the pool (:190-192).
+    """KMeanSelector (src/activelearning/kmean_selector.py:19-196): row-standardised `get_enc_feature` embeddings
+    (:95-97) and / or externally loaded features (:75-90, 101-119), sample weight = min / mean distance of each pool
+    row to the labeled rows (:143-145, 174-186) and scikit-learn's weighted k-means++ seeding over the pool (:190-192).
 
     The random numbers come from numpy's GLOBAL RandomState in sklearn's call order (one `choice`, then
     `uniform(size=2+int(log k))` per further centre), so a seeded run consumes the same stream as the reference.
-    `feature_dict` + `loaded_feature_only=True` (the demo's model-free mode, entry/demo/serve.py:125-134, with e.g.
-    BiomedCLIP features per case name) replaces the embeddings by the given rows (:86-90, 101-112).
+    Loaded features: `feature_dict` (case name -> row) or `feature_path` (one `{case}.h5` per case like the reference,
+    or `.npy` / `.npz` where h5py is missing).  With `loaded_feature_only=True` (the demo's model-free mode,
+    entry/demo/serve.py:125-134) they replace the embeddings; otherwise the standardised loaded rows are scaled by
+    sqrt(512 / D2 * loaded_feature_weight) - in float32, the reference's behaviour under its pinned numpy < 2
+    (`_cat_scale`) - and appended to the standardised embeddings (:106-121).
     Embedding, standardisation, pool-to-labeled distances and the whole seeding loop run on the GPU; the O(n)
     weight normalisation and the draws stay on the host in the reference's own numpy / torch calls.  Names are
     returned in pick order, duplicates dropped (the reference returns `list(set(...))`, :194).  Without labeled data
-    the weights are uniform (:187-188) - this selector has no random cold-start branch."""
+    the weights are uniform (:187-188) - this selector has no random cold-start branch.  Picks are bit-pinned to
+    scikit-learn 1.9.0's `_kmeans_plusplus` (fp32 sequential cumsum; <= 1.7 used a float64 `stable_cumsum`)."""
 
     def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8,
                  metric: str = "cosine", feature_path=None, feature_dict=None, coreset_criteria: str = "min",
@@ -397,29 +469,41 @@ class B200KMeanSelector(_B200Base):
             raise NotImplementedError(f"metric {metric!r}: only 'l2' and 'cosine' are supported")
         if coreset_criteria not in ("min", "mean"):
             raise RuntimeError(f"coreset_criteria {coreset_criteria} is undefined")
+        self.has_loaded = feature_path is not None or bool(feature_dict)  # `elif self.feature_dict:` (:86)
+        if loaded_feature_only and not self.has_loaded:
+            # the reference would reach np.concatenate([]) (:123) and raise there
+            raise ValueError("loaded_feature_only=True needs feature_path or feature_dict")
         if feature_path is not None:
-            raise NotImplementedError("feature_path (per-case .h5 files) is not supported: h5py is not available")
-        if (feature_dict is not None) != bool(loaded_feature_only):
-            # Mixing model and loaded features scales the latter by the numpy scalar np.sqrt(D1 / D2 * w) (:113-116):
-            # float32 under the reference's pinned numpy < 2, float64 under numpy 2 - the result dtype of the whole
-            # selection depends on the numpy version, so only the unambiguous combination is offered.
-            raise NotImplementedError("loaded features are supported as feature_dict together with "
-                                      "loaded_feature_only=True (the model-free mode of the demo)")
-        self.feature_dict, self.loaded_feature_only = feature_dict, bool(loaded_feature_only)
+            from pathlib import Path
+            feature_path = Path(feature_path)
+        self.feature_path, self.feature_dict = feature_path, feature_dict
+        self.loaded_feature_only = bool(loaded_feature_only)
         self.metric, self.coreset_criteria = metric, coreset_criteria
         self.sharp_factor, self.softmax = sharp_factor, bool(softmax)
         self.loaded_feature_weight = loaded_feature_weight
 
     def _loaded_rows(self, eng: Engine, names) -> torch.Tensor:
-        """Rows of `feature_dict` for `names`, standardised per row (:101-105) and zero-padded to the next supported
-        width (128 / 256 / 512 / 1024 columns; padding changes neither l2 nor cosine distances)."""
-        import numpy as np
-        rows = np.stack([np.asarray(self.feature_dict[n], dtype=np.float32).reshape(-1) for n in names], axis=0)
-        x = eng.standardize_rows(torch.from_numpy(rows).to(eng.device))
-        width = next((w for w in (128, 256, 512, 1024) if w >= x.shape[1]), None)
-        if width is None:
-            raise NotImplementedError(f"loaded features of dimension {x.shape[1]} (> 1024) are not supported")
-        return torch.nn.functional.pad(x, (0, width - x.shape[1])) if width != x.shape[1] else x
+        """Loaded rows for `names`, standardised per row (:101-105); on device, unpadded."""
+        # feature_path wins over feature_dict like the reference's if / elif (:75, :86)
+        rows = _loaded_feature_rows(names, None if self.feature_path is not None else self.feature_dict,
+                                    self.feature_path)
+        return eng.standardize_rows(torch.from_numpy(rows).to(eng.device))
+
+    def _features(self, eng: Engine, emb: torch.Tensor | None, names) -> torch.Tensor:
+        """get_features (:48-127) after the embedding loop: [standardised embeddings | scaled standardised loaded
+        rows], zero-padded to a kernel width."""
+        parts = []
+        if emb is not None:
+            parts.append(eng.standardize_rows(emb))
+        if self.has_loaded:
+            loaded = self._loaded_rows(eng, names)
+            if emb is not None:
+                loaded = loaded * torch.tensor(_cat_scale(emb.shape[1], loaded.shape[1], self.loaded_feature_weight),
+                                               device=eng.device)
+            parts.append(loaded)
+        x = parts[0] if len(parts) == 1 else torch.cat(parts, 1)
+        _require_finite(x, "standardised features (a constant row has std = 0)")
+        return _pad_to_kernel_width(x)
 
     def select_next_batch(self, active_dataset, select_num: int, model, device):
         import numpy as np
@@ -432,17 +516,17 @@ class B200KMeanSelector(_B200Base):
         rank, ws = D.world()
         if self.loaded_feature_only:
             eng = get_engine(device, 2, 256, 256, self.precision, 1)  # kernels only; no model involved
-            X = self._loaded_rows(eng, pool.image_idx)
-            Xl = self._loaded_rows(eng, labeled.image_idx) if labeled_size > 0 else None
+            X = self._features(eng, None, pool.image_idx)
+            Xl = self._features(eng, None, labeled.image_idx) if labeled_size > 0 else None
         else:
             lo, hi = D.shard_range(pool_size, rank, ws)
             psrc = self._source(pool, device)
             eng = self._engine(model, device, psrc.image_hw())
-            X = eng.standardize_rows(D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi)))))
+            X = self._features(eng, D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi)))), pool.image_idx)
             Xl = None
             if labeled_size > 0:
                 lsrc = self._source(labeled, device)
-                Xl = eng.standardize_rows(_embed_positions(eng, lsrc, list(range(labeled_size))))
+                Xl = self._features(eng, _embed_positions(eng, lsrc, list(range(labeled_size))), labeled.image_idx)
         if Xl is not None:
             w = eng.centre_distances(X, Xl, self.metric, self.coreset_criteria).cpu()
             if self.softmax:  # kmean_selector.py:180-183
@@ -458,10 +542,8 @@ class B200KMeanSelector(_B200Base):
         first = int(rs.choice(pool_size, p=w / w.sum()))
         uniforms = np.stack([rs.uniform(size=trials) for _ in range(select_num - 1)]) if select_num > 1 \
             else np.zeros((0, trials))
-        if ws > 1:  # every rank consumed its own stream; rank 0's draws decide so that all ranks agree
-            t = torch.from_numpy(np.concatenate([[float(first)], uniforms.reshape(-1)])).to(eng.device)
-            torch.distributed.broadcast(t, src=0)
-            first, uniforms = int(t[0].item()), t[1:].cpu().numpy().reshape(-1, trials)
+        # every rank consumed its own stream; rank 0's draws decide so that all ranks agree
+        first, uniforms = D.broadcast_draws(first, uniforms, eng.device)
         picks = eng.kmeans_pp(X, torch.from_numpy(w), first, torch.from_numpy(uniforms), select_num, trials).tolist()
         seen, out = set(), []
         for i in picks:
@@ -539,10 +621,8 @@ class B200BADGESelector(_B200Base):
         first = int(rs.choice(pool_size, p=w / w.sum()))
         uniforms = np.stack([rs.uniform(size=trials) for _ in range(select_num - 1)]) if select_num > 1 \
             else np.zeros((0, trials))
-        if D.world()[1] > 1:
-            t = torch.from_numpy(np.concatenate([[float(first)], uniforms.reshape(-1)])).to(eng.device)
-            torch.distributed.broadcast(t, src=0)
-            first, uniforms = int(t[0].item()), t[1:].cpu().numpy().reshape(-1, trials)
+        first, uniforms = D.broadcast_draws(first, uniforms, eng.device)
+        _require_finite(X, "gradient embeddings")
         picks = eng.kmeans_pp(X, torch.from_numpy(w), first, torch.from_numpy(uniforms), select_num, trials).tolist()
         return [names[i] for i in picks]  # pick order, like list(case_name_list[selected_indices]) (:126)
 
@@ -577,14 +657,17 @@ class B200HybridSelector(_B200Uncertainty):
         mine = [p for p in cand if lo <= p < hi]
         emb_c = D.gather_rows(_embed_positions(eng, psrc, mine))
         emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
-        picks = eng.kcenter(torch.cat([emb_l, emb_c], 0), labeled_size, select_num, "l2")
-        return [pool.image_idx[cand[i - labeled_size]] for i in picks.tolist()]
+        feats = torch.cat([emb_l, emb_c], 0)
+        _require_finite(feats, "embeddings")
+        picks = _check_picks(eng.kcenter(feats, labeled_size, select_num, "l2").tolist(), "k-center")
+        return [pool.image_idx[cand[i - labeled_size]] for i in picks]
 
 
 SELECTORS = {
     "b200-entropy": B200EntropySelector,
     "b200-margin": B200MarginSelector,
     "b200-confidence": B200ConfidenceSelector,
+    "b200-dice": B200DiceUncertaintySelector,
     "b200-mc-entropy": B200MCDropoutEntropySelector,
     "b200-coreset-l2": lambda **kw: B200CoresetSelector(metric="l2", **kw),
     "b200-coreset-cosine": lambda **kw: B200CoresetSelector(metric="cosine", **kw),

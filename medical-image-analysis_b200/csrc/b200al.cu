@@ -96,6 +96,7 @@ struct b200al_ctx {
   bool fuse_head = false;
   double* partial = nullptr;
   int partial_blocks = 0;
+  double* dice_partial = nullptr;  // [max_samples][kDiceBlocks][3 * kMaxClasses]
   double* badge_stats = nullptr;  // [max_samples][kBadgeBlocks][3K]
   double* badge_grad = nullptr;   // [max_samples][kBadgeBlocks][K*32]
   float* badge_coef = nullptr;    // [max_samples][2K]
@@ -705,11 +706,12 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
   TRY_RC(dev_alloc(ctx, &ctx->mask, (size_t)max_samples * B200AL_MASK_CHANNELS));
   ctx->partial_blocks = 64;
   TRY_RC(dev_alloc(ctx, &ctx->partial, (size_t)max_samples * ctx->partial_blocks));
+  TRY_RC(dev_alloc(ctx, &ctx->dice_partial, (size_t)max_samples * kDiceBlocks * 3 * kMaxClasses));
   TRY_RC(dev_alloc(ctx, &ctx->prep_partials, (size_t)max_samples * ((ctx->H + kPrepBand - 1) / kPrepBand) * 2));
   ctx->kc_blocks = ctx->sm_count * 4;
   TRY_RC(dev_alloc(ctx, &ctx->kc_part_val, (size_t)ctx->kc_blocks));
   TRY_RC(dev_alloc(ctx, &ctx->kc_part_idx, (size_t)ctx->kc_blocks));
-  TRY_RC(dev_alloc(ctx, &ctx->kc_centre, 1024));
+  TRY_RC(dev_alloc(ctx, &ctx->kc_centre, 2048));
   TRY_RC(dev_alloc(ctx, &ctx->tk_state, 1));
   fill_kernel<<<2, 256>>>(ctx->ones, 1.0f, 512);
   fill_kernel<<<2, 256>>>(ctx->zeros, 0.0f, 512);
@@ -867,6 +869,16 @@ void launch_unc(const float* logits, int n, int T, int HW, int mode, float smoot
   uncertainty_logits_kernel<K><<<grid, 256, 0, st>>>(logits, T, HW, mode, smooth, partial);
 }
 
+// dice-uncertainty over fp32 logits [n][T][K][HW]: 3K sums per image, then the DiceLoss formula (uncertainty.cuh)
+template <int K>
+void launch_dice(const float* logits, int n, int T, int HW, float smooth, double* partial, float* scores,
+                 cudaStream_t st) {
+  int nblk = (HW / 4 + 255) / 256;
+  if (nblk > kDiceBlocks) nblk = kDiceBlocks;
+  dice_logits_kernel<K><<<dim3(nblk, n), 256, 0, st>>>(logits, T, HW, partial);
+  dice_finalize_kernel<K><<<(n + 127) / 128, 128, 0, st>>>(partial, nblk, smooth, scores, n);
+}
+
 #define DISPATCH_K(K_, CALL)                         \
   switch (K_) {                                      \
     case 2: CALL(2); break;                          \
@@ -926,9 +938,13 @@ extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int ima
   if (!d_images || !d_scores_out || n < 0 || T < 1) return set_err(ctx, B200AL_ERR_ARG, "bad argument");
   if ((long long)n * T > ctx->max_samples)
     return set_err(ctx, B200AL_ERR_ARG, "n*T = %lld exceeds max_samples = %d", (long long)n * T, ctx->max_samples);
-  if (mode < 0 || mode > 2) return set_err(ctx, B200AL_ERR_ARG, "bad score mode %d", mode);
+  if (mode < 0 || mode > 3) return set_err(ctx, B200AL_ERR_ARG, "bad score mode %d", mode);
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (mode == B200AL_DICE && !ctx->fuse_head && !d_logits_out && !ctx->logits_buf) {
+    // unfused head (K > 4): the dice reduction reads logits, so they need a home; allocated on first use
+    if (int rc0 = dev_alloc(ctx, &ctx->logits_buf, (size_t)ctx->max_samples * ctx->K * ctx->H * ctx->W)) return rc0;
+  }
   const float* mask = nullptr;
   int rc = prepare_masks(ctx, n, T, drop_p, mc_seed, base_pos, d_drop_masks, &mask, st);
   if (rc) return rc;
@@ -941,14 +957,31 @@ extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int ima
     if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st, lg))) return rc;
     const int HW = ctx->H * ctx->W;
     if ((HW / 4 + 255) / 256 < nblk) nblk = (HW / 4 + 255) / 256;
+    if (mode == B200AL_DICE) {
+#define CALL_DICE(KK) launch_dice<KK>(lg, n, T, HW, smooth, ctx->dice_partial, d_scores_out, st)
+      DISPATCH_K(ctx->K, CALL_DICE)
+#undef CALL_DICE
+      ctx->launches += 2;
+      CUDA_TRY(ctx, cudaGetLastError());
+      return B200AL_OK;
+    }
 #define CALL_UNC(KK) launch_unc<KK>(lg, n, T, HW, mode, smooth, ctx->partial, nblk, st)
     DISPATCH_K(ctx->K, CALL_UNC)
 #undef CALL_UNC
   } else {
     if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st))) return rc;
-#define CALL_HEAD(KK) launch_head<KK>(ctx, n, T, mode, smooth, d_logits_out, st)
+    float* lg = mode == B200AL_DICE ? (d_logits_out ? d_logits_out : ctx->logits_buf) : d_logits_out;
+#define CALL_HEAD(KK) launch_head<KK>(ctx, n, T, mode == B200AL_DICE ? 0 : mode, smooth, lg, st)
     DISPATCH_K(ctx->K, CALL_HEAD)
 #undef CALL_HEAD
+    if (mode == B200AL_DICE) {
+#define CALL_DICE(KK) launch_dice<KK>(lg, n, T, ctx->H * ctx->W, smooth, ctx->dice_partial, d_scores_out, st)
+      DISPATCH_K(ctx->K, CALL_DICE)
+#undef CALL_DICE
+      ctx->launches += 3;
+      CUDA_TRY(ctx, cudaGetLastError());
+      return B200AL_OK;
+    }
   }
   uncertainty_finalize_kernel<<<(n + 127) / 128, 128, 0, st>>>(ctx->partial, nblk, ctx->H * ctx->W, d_scores_out, n);
   ctx->launches += 2;
@@ -1030,7 +1063,7 @@ extern "C" int b200al_uncertainty_from_logits(b200al_ctx* ctx, const float* d_lo
   if (n == 0) return B200AL_OK;
   if (!d_logits || !d_scores_out || n < 0 || T < 1 || K < 2 || K > kMaxClasses || HW < 4 || HW % 4)
     return set_err(ctx, B200AL_ERR_ARG, "bad argument (need 2 <= K <= %d, HW %% 4 == 0)", kMaxClasses);
-  if (mode < 0 || mode > 2) return set_err(ctx, B200AL_ERR_ARG, "bad score mode %d", mode);
+  if (mode < 0 || mode > 3) return set_err(ctx, B200AL_ERR_ARG, "bad score mode %d", mode);
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
   int nblk = (HW / 4 + 255) / 256;
@@ -1038,6 +1071,13 @@ extern "C" int b200al_uncertainty_from_logits(b200al_ctx* ctx, const float* d_lo
   for (int i0 = 0; i0 < n; i0 += ctx->max_samples) {
     const int nn = (n - i0) < ctx->max_samples ? (n - i0) : ctx->max_samples;
     const float* lg = d_logits + (size_t)i0 * T * K * HW;
+    if (mode == B200AL_DICE) {
+#define CALL_DICE(KK) launch_dice<KK>(lg, nn, T, HW, smooth, ctx->dice_partial, d_scores_out + i0, st)
+      DISPATCH_K(K, CALL_DICE)
+#undef CALL_DICE
+      ctx->launches += 2;
+      continue;
+    }
 #define CALL_UNC(KK) launch_unc<KK>(lg, nn, T, HW, mode, smooth, ctx->partial, nblk, st)
     DISPATCH_K(K, CALL_UNC)
 #undef CALL_UNC
@@ -1092,9 +1132,9 @@ template <int NV>
 void launch_kc_init(const float* emb, int n, const float* centres, int L, int metric, int criteria, void* state,
                     int accumulate, int blocks, cudaStream_t st) {
   if (criteria == B200AL_MEAN)
-    kcenter_init_mean_kernel<NV, (NV <= 4 ? 4 : 2)><<<blocks, 256, 0, st>>>(emb, n, centres, L, metric, (double*)state, accumulate);
+    kcenter_init_mean_kernel<NV, (NV <= 4 ? 4 : NV <= 8 ? 2 : 1)><<<blocks, 256, 0, st>>>(emb, n, centres, L, metric, (double*)state, accumulate);
   else
-    kcenter_init_kernel<NV, (NV <= 4 ? 4 : 2)><<<blocks, 256, 0, st>>>(emb, n, centres, L, metric, (float*)state, accumulate);
+    kcenter_init_kernel<NV, (NV <= 4 ? 4 : NV <= 8 ? 2 : 1)><<<blocks, 256, 0, st>>>(emb, n, centres, L, metric, (float*)state, accumulate);
 }
 template <int NV>
 void launch_kc_step(const float* emb, int n, const float* centre, int do_update, int metric, int criteria, void* state,
@@ -1105,8 +1145,8 @@ void launch_kc_step(const float* emb, int n, const float* centre, int do_update,
     kcenter_step_kernel<NV><<<blocks, 256, 0, st>>>(emb, n, centre, do_update, metric, (float*)state, taken, pv, pi);
 }
 int check_dim(b200al_ctx* ctx, int D) {
-  if (D != 128 && D != 256 && D != 512 && D != 1024)
-    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "embedding dim %d not in {128,256,512,1024}", D);
+  if (D != 128 && D != 256 && D != 512 && D != 1024 && D != 1536 && D != 2048)
+    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "row width %d not in {128,256,512,1024,1536,2048}", D);
   return 0;
 }
 }  // namespace
@@ -1140,6 +1180,8 @@ extern "C" int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, i
     case 2: launch_kc_init<2>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
     case 4: launch_kc_init<4>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
     case 8: launch_kc_init<8>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
+    case 12: launch_kc_init<12>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
+    case 16: launch_kc_init<16>(d_emb, n, d_centres, L, metric, criteria, d_state, accumulate, blocks, st); break;
   }
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
@@ -1275,6 +1317,8 @@ extern "C" int b200al_kmeans_pp(b200al_ctx* ctx, const float* d_X, int n, int D,
     case 2: kmpp_norms_kernel<2><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
     case 4: kmpp_norms_kernel<4><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
     case 8: kmpp_norms_kernel<8><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
+    case 12: kmpp_norms_kernel<12><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
+    case 16: kmpp_norms_kernel<16><<<blocks, 256, 0, st>>>(d_X, n, xx); break;
   }
   ctx->launches++;
 #define KMPP_DIST(TR, FIRST)                                                                                   \
@@ -1283,6 +1327,8 @@ extern "C" int b200al_kmeans_pp(b200al_ctx* ctx, const float* d_X, int n, int D,
     case 2: launch_kmpp_dist<2>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
     case 4: launch_kmpp_dist<4>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
     case 8: launch_kmpp_dist<8>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 12: launch_kmpp_dist<12>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
+    case 16: launch_kmpp_dist<16>(d_X, xx, d_weight, n, cand, TR, closest, FIRST, cand_d, part, blocks, st); break;   \
   }
   kmpp_set_first_kernel<<<1, 1, 0, st>>>(cand, first_centre);
   KMPP_DIST(1, 1)
@@ -1324,6 +1370,8 @@ extern "C" int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, in
       case 2: launch_kc_step<2>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
       case 4: launch_kc_step<4>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
       case 8: launch_kc_step<8>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 12: launch_kc_step<12>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
+      case 16: launch_kc_step<16>(d_emb, n, ctx->kc_centre, upd, metric, criteria, d_state, inv, d_taken, ctx->kc_part_val, ctx->kc_part_idx, blocks, st); break;
     }
     kcenter_pick_kernel<<<1, 256, 0, st>>>(ctx->kc_part_val, ctx->kc_part_idx, blocks, d_emb, D, d_taken,
                                           ctx->kc_centre, (long long*)d_picks, d_pick_vals, step);

@@ -16,7 +16,8 @@
 
 namespace b200al {
 
-enum { MODE_ENTROPY = 0, MODE_MARGIN = 1, MODE_CONFIDENCE = 2 };
+enum { MODE_ENTROPY = 0, MODE_MARGIN = 1, MODE_CONFIDENCE = 2, MODE_DICE = 3 };
+constexpr int kDiceBlocks = 32;  // partial blocks per image of the dice-uncertainty reduction
 constexpr int kMaxClasses = 8;
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -203,6 +204,95 @@ head_uncertainty_kernel(const __nv_bfloat16* __restrict__ feat, int pitch, int h
   }
   const double r = block_sum(acc);
   if (threadIdx.x == 0) partial[(size_t)img * gridDim.x + blockIdx.x] = r;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Dice-uncertainty (north-star kernel 3, third mode): score = DiceLoss(pbar, one_hot(argmax_k pbar)) with
+// the reference's DiceLoss semantics (src/losses/dice_loss.py:32-72: do_bg = True, batch = False, squared = False):
+//   I_c = sum_px pbar_c * y_c,  P_c = sum_px pbar_c,  Y_c = sum_px y_c,
+//   score = mean_c ( 1 - (2 I_c + smooth) / (P_c + Y_c + smooth) ).
+// One pass over the logits like the other modes, but 3K running sums per image instead of one; the non-linear part
+// runs in the finalize kernel on the per-image totals.  partial: [n][gridDim.x][3K] doubles.
+template <int K>
+__global__ void __launch_bounds__(256)
+dice_logits_kernel(const float* __restrict__ logits, int T, int HW, double* __restrict__ partial) {
+  const int img = blockIdx.y;
+  const float* base = logits + (size_t)img * T * K * HW;
+  float accI[K], accP[K], accY[K];
+#pragma unroll
+  for (int k = 0; k < K; ++k) accI[k] = accP[k] = accY[k] = 0.f;
+  const float inv_T = 1.0f / (float)T;
+  for (int p4 = (blockIdx.x * blockDim.x + threadIdx.x) * 4; p4 < HW; p4 += gridDim.x * blockDim.x * 4) {
+    float pbar[4][K];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+#pragma unroll
+      for (int k = 0; k < K; ++k) pbar[j][k] = 0.f;
+    for (int t = 0; t < T; ++t) {
+      float4 v[K];
+#pragma unroll
+      for (int k = 0; k < K; ++k)
+        v[k] = __ldg(reinterpret_cast<const float4*>(base + ((size_t)t * K + k) * HW + p4));
+      float l[K];
+#pragma unroll
+      for (int k = 0; k < K; ++k) l[k] = v[k].x;
+      softmax_accum<K>(l, pbar[0]);
+#pragma unroll
+      for (int k = 0; k < K; ++k) l[k] = v[k].y;
+      softmax_accum<K>(l, pbar[1]);
+#pragma unroll
+      for (int k = 0; k < K; ++k) l[k] = v[k].z;
+      softmax_accum<K>(l, pbar[2]);
+#pragma unroll
+      for (int k = 0; k < K; ++k) l[k] = v[k].w;
+      softmax_accum<K>(l, pbar[3]);
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      int am = 0;
+      float best = pbar[j][0];
+#pragma unroll
+      for (int k = 1; k < K; ++k)
+        if (pbar[j][k] > best) { best = pbar[j][k]; am = k; }  // first maximum, like torch.argmax
+#pragma unroll
+      for (int k = 0; k < K; ++k) {
+        const float p = T > 1 ? pbar[j][k] * inv_T : pbar[j][k];
+        accP[k] += p;
+        if (k == am) { accI[k] += p; accY[k] += 1.f; }
+      }
+    }
+  }
+  // a thread adds at most HW / (4 * 256) * 4 terms in fp32 (<= 256 at 256^2 with one block); the rest is fp64
+  double* out = partial + ((size_t)img * gridDim.x + blockIdx.x) * 3 * K;
+#pragma unroll
+  for (int k = 0; k < K; ++k) {
+    double r = block_sum((double)accI[k]);
+    if (threadIdx.x == 0) out[k] = r;
+    __syncthreads();
+    r = block_sum((double)accP[k]);
+    if (threadIdx.x == 0) out[K + k] = r;
+    __syncthreads();
+    r = block_sum((double)accY[k]);
+    if (threadIdx.x == 0) out[2 * K + k] = r;
+    __syncthreads();
+  }
+}
+
+template <int K>
+__global__ void dice_finalize_kernel(const double* __restrict__ partial, int nblk, float smooth,
+                                     float* __restrict__ scores, int n) {
+  const int img = blockIdx.x * blockDim.x + threadIdx.x;
+  if (img >= n) return;
+  double loss = 0.0;
+  for (int k = 0; k < K; ++k) {
+    double I = 0.0, P = 0.0, Y = 0.0;
+    for (int b = 0; b < nblk; ++b) {
+      const double* p = partial + ((size_t)img * nblk + b) * 3 * K;
+      I += p[k]; P += p[K + k]; Y += p[2 * K + k];
+    }
+    loss += 1.0 - (2.0 * I + (double)smooth) / (P + Y + (double)smooth);
+  }
+  scores[img] = (float)(loss / (double)K);
 }
 
 }  // namespace b200al

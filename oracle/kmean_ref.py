@@ -106,3 +106,28 @@ def kmean_select(pool_emb, labeled_emb, select_num, metric="cosine", criteria="m
     lab = standardize_rows(labeled_emb) if labeled_emb is not None and len(labeled_emb) else None
     w = sample_weights(pool, lab, metric, criteria, sharp_factor, softmax)
     return kmeans_plusplus_indices(pool, select_num, w, rs, return_gap)
+
+
+def kmean_features(emb, loaded, weight: float = 1.0, numpy_rule: str = "legacy") -> np.ndarray:
+    """KMeanSelector.get_features after the loops (kmean_selector.py:92-125): [standardised embeddings |
+    standardised loaded rows * np.sqrt(D1 / D2 * loaded_feature_weight)]; either part may be None
+    (`loaded_feature_only`, or no loaded features).  numpy_rule: see oracle.select_ref.cat_scale."""
+    from .select_ref import cat_scale
+    parts = []
+    if emb is not None:
+        parts.append(standardize_rows(emb))
+    if loaded is not None:
+        lf = standardize_rows(loaded)
+        parts.append(lf if emb is None else lf * cat_scale(np.shape(emb)[1], lf.shape[1], weight, numpy_rule))
+    return np.concatenate(parts, axis=1)
+
+
+def kmean_mix_select(pool_emb, labeled_emb, pool_loaded, labeled_loaded, weight, select_num, metric="cosine",
+                     criteria="min", sharp_factor=1.0, softmax=False, random_state=None, return_gap=False):
+    """KMeanSelector.select_next_batch with model AND loaded features under the reference's numpy < 2 rule (float32
+    throughout): pool positions in pick order."""
+    rs = np.random.mtrand._rand if random_state is None else random_state
+    pool = kmean_features(pool_emb, pool_loaded, weight)
+    lab = kmean_features(labeled_emb, labeled_loaded, weight) if labeled_emb is not None and len(labeled_emb) else None
+    w = sample_weights(pool, lab, metric, criteria, sharp_factor, softmax)
+    return kmeans_plusplus_indices(pool, select_num, w, rs, return_gap)

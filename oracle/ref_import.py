@@ -71,7 +71,7 @@ def load_reference() -> SimpleNamespace:
         return _cache
     if not reference_available():
         raise RuntimeError(f"reference sources not found at {REFERENCE_SRC}")
-    for generic in ("datasets", "models", "utils", "transforms", "activelearning"):
+    for generic in ("datasets", "models", "utils", "transforms", "activelearning", "losses"):
         m = sys.modules.get(generic)
         if m is not None and not str(getattr(m, "__file__", "")).startswith(REFERENCE_SRC):
             raise RuntimeError(
@@ -92,6 +92,7 @@ def load_reference() -> SimpleNamespace:
         cs = importlib.import_module("activelearning.coreset_selector")
         norm = importlib.import_module("transforms.normalization")
         jt = importlib.import_module("transforms.joint_transform")
+        dl = importlib.import_module("losses.dice_loss")
     finally:
         sys.path.remove(REFERENCE_SRC)
     _cache = SimpleNamespace(
@@ -111,6 +112,7 @@ def load_reference() -> SimpleNamespace:
         BUSIDataset=ds.BUSIDataset,
         ZScoreNormalize=norm.ZScoreNormalize,
         JointResize=jt.JointResize,
+        DiceLoss=dl.DiceLoss,
     )
     return _cache
 

@@ -46,10 +46,33 @@ def scores_from_prob(prob: torch.Tensor, mode: str, smooth: float = SMOOTH) -> t
         return (-1 * (top2[:, 0] - top2[:, 1])).mean(dim=[-2, -1])
     if mode == "confidence":
         return (-1 * prob.max(1)[0]).mean(dim=[-2, -1])
+    if mode == "dice":
+        return dice_scores_from_prob(prob)
     raise ValueError(mode)
 
 
-SCORE_FNS = {"entropy": entropy_scores, "margin": margin_scores, "confidence": confidence_scores}
+DICE_SMOOTH = 1e-5  # DiceLoss(smooth) as al_train builds it (al_trainer.py:785-791)
+
+
+def dice_scores_from_prob(prob: torch.Tensor, smooth: float = DICE_SMOOTH) -> torch.Tensor:
+    """Dice-uncertainty (named by BASELINE.json's north star, absent from the reference's selectors):
+    per image, DiceLoss of the probability map against its own hard prediction, following DiceLoss.forward
+    (src/losses/dice_loss.py:32-72) with do_bg=True, batch=False, squared=False: one-hot of argmax (:24-30),
+    intersect / sum_inputs / sum_targets over the pixel axes (:62-64), `1 - (2I + s) / (P + Y + s)` per class (:71),
+    mean over classes (:75) - evaluated per image (B = 1) so that each image gets its own score."""
+    y = torch.zeros_like(prob).scatter_(1, prob.argmax(1, keepdim=True), 1.0)
+    axes = tuple(range(2, prob.ndim))
+    intersect = (prob * y).sum(axes)
+    dice = 1 - (2 * intersect + smooth) / (prob.sum(axes) + y.sum(axes) + smooth)
+    return dice.mean(1)
+
+
+def dice_scores(logits: torch.Tensor, smooth: float = DICE_SMOOTH) -> torch.Tensor:
+    return dice_scores_from_prob(logits.softmax(1), smooth)
+
+
+SCORE_FNS = {"entropy": entropy_scores, "margin": margin_scores, "confidence": confidence_scores,
+             "dice": dice_scores}
 
 
 def rank_desc_stable(scores, k: int) -> np.ndarray:
@@ -310,4 +333,77 @@ def kcenter_fused_add_stream(feats: np.ndarray, loaded: np.ndarray, weight: floa
         taken[q] = True
         picks.append(q)
         state = state + fused(q) if criteria == "mean" else np.minimum(state, fused(q))
+    return (picks, gaps) if return_gaps else picks
+
+
+# ---------------------------------------------------------------------------
+# coreset_fusion="cat" (coreset_selector.py:158-175) / KMeanSelector's model + loaded mix (kmean_selector.py:106-121)
+# ---------------------------------------------------------------------------
+def cat_scale(d1: int, d2: int, weight: float, numpy_rule: str = "legacy"):
+    """`scale_factor = np.sqrt(D1 / D2 * loaded_feature_weight)` - an np.float64 scalar - as the factor the reference's
+    `loaded_feats * scale_factor` multiplies with.  The reference pins numpy < 2 (pyproject.toml:21): value-based
+    casting keeps `float32_array * float64_scalar` in float32, the scalar is cast to float32 first ("legacy", what the
+    product path implements).  Under numpy >= 2 (NEP 50; 2.3.5 is what this image has) the same line promotes the
+    array to float64 ("nep50"; used only to pin the restatement against the reference run live here)."""
+    s = np.sqrt(d1 / d2 * weight)
+    return np.float32(s) if numpy_rule == "legacy" else np.float64(s)
+
+
+def coreset_cat_rows(feats: np.ndarray, loaded: np.ndarray, weight: float, numpy_rule: str = "legacy") -> np.ndarray:
+    """final_feats of the "cat" branch (:160-174): [feats | loaded * scale]; float32 under the legacy rule, float64
+    under NEP 50 (np.concatenate promotes)."""
+    feats = np.asarray(feats, np.float32)
+    loaded = np.asarray(loaded, np.float32)
+    return np.concatenate([feats, loaded * cat_scale(feats.shape[1], loaded.shape[1], weight, numpy_rule)], axis=1)
+
+
+def coreset_cat_select(feats, loaded, weight, n_init, budget, metric="l2", criteria="min", numpy_rule="legacy",
+                       return_gaps=False):
+    """k-center greedy over the concatenated rows (:175, then :221-229).  Under "nep50" the rows are float64 and
+    sklearn's euclidean_distances skips the float32 upcast path: plain fp64 distances, fp64 sqrt."""
+    rows = coreset_cat_rows(feats, loaded, weight, numpy_rule)
+    if rows.dtype == np.float64:
+        def l2_64(f, c, j):
+            x = f.astype(np.float64)
+            d2 = np.maximum((x * x).sum(1) + (c * c).sum() - 2.0 * (x @ c), 0)
+            d2[j] = 0
+            return np.sqrt(d2)
+
+        def cos_64(f, c, j):
+            d = np.clip(1.0 - f @ c, 0, 2)
+            d[j] = 0
+            return d
+        if metric == "l2":
+            f, fn = rows, l2_64
+        else:
+            nr = np.sqrt((rows * rows).sum(1))
+            nr[nr == 0] = 1
+            f, fn = rows / nr[:, None], cos_64
+        return _kcenter_generic(f, n_init, budget, fn, criteria, return_gaps)
+    if criteria == "mean":
+        return kcenter_greedy_mean_stream(rows, n_init, budget, metric, return_gaps)
+    return kcenter_greedy_stream(rows, n_init, budget, metric, return_gaps=return_gaps)
+
+
+def _kcenter_generic(f, n_init, budget, fn, criteria, return_gaps):
+    n = f.shape[0]
+    state = np.zeros(n) if criteria == "mean" else np.full(n, np.inf)
+    for j in range(n_init):
+        d = fn(f, f[j], j)
+        state = state + d if criteria == "mean" else np.minimum(state, d)
+    taken = np.zeros(n, dtype=bool)
+    taken[:n_init] = True
+    picks, gaps = [], []
+    for step in range(budget):
+        val = state / float(n_init + step) if criteria == "mean" else state
+        cand = np.where(taken, -np.inf, val)
+        q = int(cand.argmax())
+        if return_gaps:
+            top = cand[q]
+            cand[q] = -np.inf
+            gaps.append(float(top - cand.max()) if n - taken.sum() > 1 else float("inf"))
+        taken[q] = True
+        picks.append(q)
+        d = fn(f, f[q], q)
+        state = state + d if criteria == "mean" else np.minimum(state, d)
     return (picks, gaps) if return_gaps else picks

@@ -87,8 +87,12 @@ def test_selector_ctor_contract():
     assert b200al.B200CoresetSelector(8, 0, coreset_criteria="mean").coreset_criteria == "mean"
     with pytest.raises(RuntimeError, match="undefined"):   # coreset_selector.py:38-40
         b200al.B200CoresetSelector(8, 0, coreset_criteria="median")
+    assert str(b200al.B200CoresetSelector(8, 0, feature_path="/tmp/x", coreset_fusion="cat").feature_path) == "/tmp/x"
     with pytest.raises(NotImplementedError):
-        b200al.B200CoresetSelector(8, 0, feature_path="/tmp/x")
+        b200al.B200CoresetSelector(8, 0, coreset_fusion="mul")
+    with pytest.raises(ValueError):
+        b200al.B200KMeanSelector(8, 0, loaded_feature_only=True)
+    assert b200al.B200DiceUncertaintySelector(8, 0).smooth == 1e-5
     for name, ctor in b200al.SELECTORS.items():
         assert isinstance(ctor(batch_size=4, num_workers=0, pin_memory=False), b200al.ActiveSelector), name
 
@@ -152,9 +156,45 @@ def test_install_into_al_trainer_shim():
     t._setup_active_selector()
     assert isinstance(t.active_selector, b200al.B200CoresetSelector)
     assert (t.active_selector.metric, t.active_selector.coreset_criteria) == ("l2", "mean")
+    # al_trainer.py:845-870 also hands feature_path / loaded_feature_weight / loaded_feature_only to KMeanSelector
+    t.config.active_selector_name = "b200-kmean-cosine"
+    t.config.feature_path, t.config.loaded_feature_weight, t.config.loaded_feature_only = "/tmp/feats", 0.3, True
+    t.config.kmean_sharp_factor, t.config.kmean_softmax = 2.0, True
+    t._setup_active_selector()
+    k = t.active_selector
+    assert isinstance(k, b200al.B200KMeanSelector) and str(k.feature_path) == "/tmp/feats"
+    assert (k.loaded_feature_weight, k.loaded_feature_only, k.sharp_factor, k.softmax) == (0.3, True, 2.0, True)
+    t.config.feature_path = None   # loaded_feature_only without any loaded features: refused, not silently ignored
+    with pytest.raises(ValueError):
+        t._setup_active_selector()
     t.config.active_selector_name = "nope"
     with pytest.raises(ValueError):
         t._setup_active_selector()
+
+
+def test_loaded_feature_files_and_cat_scale(tmp_path):
+    """feature_path rows from .npy / .npz files (the .h5 stand-in where h5py is absent) and the float32 scale of
+    the "cat" / mix paths (numpy < 2 rule of the reference, pyproject.toml:21)."""
+    from b200al import selectors as SM
+    from oracle.select_ref import cat_scale
+    rows = {"a": np.arange(5, dtype=np.float32), "b": np.ones(5, np.float64)}
+    np.save(tmp_path / "a.npy", rows["a"])
+    np.savez(tmp_path / "b.npz", feature=rows["b"])
+    got = SM._loaded_feature_rows(["b", "a"], None, tmp_path)
+    assert got.dtype == np.float32 and got.tolist() == [rows["b"].tolist(), rows["a"].tolist()]
+    with pytest.raises(FileNotFoundError):
+        SM._loaded_feature_rows(["c"], None, tmp_path)
+    for d1, d2, w in ((512, 200, 0.4), (512, 512, 1.0), (512, 700, 0.05)):
+        s = SM._cat_scale(d1, d2, w)
+        assert isinstance(s, np.float32) and s == cat_scale(d1, d2, w, "legacy") == np.float32(np.sqrt(d1 / d2 * w))
+    x = torch.zeros(3, 712)
+    assert SM._pad_to_kernel_width(x).shape == (3, 1024) and SM._pad_to_kernel_width(torch.zeros(2, 1212)).shape == (2, 1536)
+    with pytest.raises(NotImplementedError):
+        SM._pad_to_kernel_width(torch.zeros(1, 4096))
+    with pytest.raises(RuntimeError, match="non-finite"):
+        SM._require_finite(torch.tensor([1.0, float("nan")]), "embeddings")
+    with pytest.raises(RuntimeError):
+        SM._check_picks([3, -1], "k-center")
 
 
 def test_pool_source_serves_cached_rows_in_pool_order():

@@ -270,3 +270,47 @@ def test_fused_coreset_oracle_matches_reference_live(ref, golden, tmp_path, monk
         want = sel.select_next_batch(make_active(images, 5, reference=ref), 6, model, torch.device("cpu"))
         picks = S.kcenter_fused_add_stream(emb, loaded, w, 5, 6, metric, crit)
         assert sorted(map(str, want)) == sorted(names[i] for i in picks)
+
+
+def test_dice_oracle_matches_reference_diceloss_class(ref):
+    """Dice-uncertainty = the reference's DiceLoss (src/losses/dice_loss.py:32-72, configured like
+    al_trainer.py:785-791 but do_bg=True) of each image's softmax map against its own argmax."""
+    from oracle import select_ref as S
+    g = torch.Generator().manual_seed(5)
+    for K in (2, 3, 4):
+        logits = torch.randn(5, K, 40, 24, generator=g) * 2
+        loss = ref.DiceLoss(num_classes=K - 1, smooth=1e-5, do_bg=True, softmax=True)
+        want = torch.stack([loss(logits[i:i + 1], logits[i:i + 1].softmax(1).argmax(1)) for i in range(5)])
+        got = S.dice_scores(logits)
+        np.testing.assert_allclose(got.numpy(), want.numpy(), rtol=1e-6, atol=1e-7)
+
+
+def test_cat_fusion_restatement_matches_reference_live(ref, golden, tmp_path, monkeypatch):
+    """coreset_fusion="cat" run live (numpy 2 here -> float64 product) == the restatement under the same rule; the
+    product path implements the reference's pinned numpy < 2 rule (float32), which cannot be run live here."""
+    import importlib
+    from oracle import select_ref as S
+    from oracle.make_golden_fused import H5Shim, write_feature_files
+    from oracle.ref_import import build_reference_unet
+    from oracle.synth import make_active, synth_pool_u8
+    from oracle.unet_ref import golden_state_dict
+    cs = importlib.import_module("activelearning.coreset_selector")
+    monkeypatch.setattr(cs, "h5py", H5Shim, raising=False)
+    sd = golden_state_dict(3, golden["model"])
+    model = build_reference_unet(3)
+    model.load_state_dict(sd)
+    images = synth_pool_u8(4 + 14, start=300)
+    ad = make_active(images, 4, reference=ref)
+    names = list(ad.get_train_dataset().image_idx) + list(ad.get_pool_dataset().image_idx)
+    rng = np.random.default_rng(3)
+    fd = {n: rng.standard_normal(96).astype(np.float32) for n in names}
+    write_feature_files(str(tmp_path), fd)
+    loaded = np.stack([fd[n] for n in names])
+    emb = S.pool_embeddings(sd, images)
+    for metric in ("l2", "cosine"):
+        sel = ref.CoresetSelector(batch_size=8, num_workers=0, pin_memory=False, metric=metric, coreset_fusion="cat",
+                                  feature_path=str(tmp_path), loaded_feature_weight=0.6)
+        live = sel.select_next_batch(make_active(images, 4, reference=ref), 5, model, torch.device("cpu"))
+        rule = "nep50" if int(np.__version__.split(".")[0]) >= 2 else "legacy"
+        picks = S.coreset_cat_select(emb, loaded, 0.6, 4, 5, metric, "min", rule)
+        assert sorted(map(str, live)) == sorted(names[i] for i in picks)
