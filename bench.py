@@ -3,24 +3,27 @@
   python bench.py --gpus N --steps K --warmup W            (our arm)
   python bench.py --impl reference --gpus N --steps K ...  (CPU reference arm)
 
-Workload at every N = BASELINE.json configs[1]: UNet MC-dropout (T=8) entropy
-acquisition on a FUGC-shape (1x256x256, K=3) synthetic pool, 10 000 images per
-GPU, budget 100.  One step = one full acquisition pass over the rank's pool
-(score every image, rank, cut) plus, for N > 1, the all-gather + merge of the
-per-rank top-k candidates.  Weak scaling: each rank owns its own 10k shard.
+Workload at every N = BASELINE.json configs[1]: UNet MC-dropout (T=8) entropy acquisition on ONE FUGC-shape
+(1x256x256, K=3) synthetic pool of 10 000 images, budget 100, through the public drop-in call
+`B200MCDropoutEntropySelector.select_next_batch`.  For N > 1 the ranks run the same call under the NCCL process
+group: the pool is sharded into contiguous position ranges (STRONG scaling - the total work is fixed), every rank
+scores its shard, and only the per-rank top-k candidates are all-gathered and merged.  One step = one full
+`select_next_batch`: weight broadcast + fold/pack, MC masks, forward, uncertainty reduction, rank & cut, merge,
+position -> name mapping.
 
-value  : images/s with the uint8 pool already resident in HBM.
-e2e    : the same pass through the drop-in selector (`select_next_batch`) with
-         the pool in pinned HOST memory: per-chunk H2D copies and the D2H read
-         of the selected positions are inside the timed region.
-roofline: the tcgen05 conv kernels (all layers), CUDA-event timed per launch
-         inside the library during the timed steps.
-cpu_baseline: the oracle port (torch fp32 restatement of the reference path) on
-         the host cores, on a bounded sample.
+value  : images/s with the uint8 pool already resident in HBM (the dataset's `images_u8` is a CUDA tensor).
+e2e    : the same call with the pool in pinned HOST memory: per-chunk H2D copies of the rank's shard and the D2H
+         read of the selected positions are inside the timed region.
+roofline: the tcgen05 conv kernels (all 21 layers), CUDA-event timed per launch inside the library during the
+         timed steps of the `value` arm.
+config4: secondary record - BASELINE.json configs[3], hybrid entropy -> k-center over a 100k-image pool, budget 500,
+         through `B200HybridSelector.select_next_batch` (seconds, images/s, stage breakdown, hash of the picks).
+cpu_baseline: the oracle port (torch fp32 restatement of the reference path) on the host cores, bounded sample.
 """
 from __future__ import annotations
 
 import argparse
+import hashlib
 import json
 import os
 import subprocess
@@ -31,13 +34,14 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path[:0] = [ROOT, os.path.join(ROOT, "medical-image-analysis_b200")]
 
-POOL_PER_GPU = 10_000
+POOL = 10_000
 T_REPEATS = 8
 DROP_P = 0.1
 BUDGET = 100
 K_CLASSES = 3
 MC_SEED = 2025
 METRIC = "pool images/sec scored+selected"
+C4_POOL, C4_LABELED, C4_BUDGET = 100_000, 500, 500
 
 
 def parse():
@@ -46,12 +50,14 @@ def parse():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--pool", type=int, default=POOL_PER_GPU, help="images per GPU")
+    ap.add_argument("--pool", type=int, default=POOL, help="images in the (one, sharded) pool")
     ap.add_argument("--chunk", type=int, default=int(os.environ.get("B200AL_CHUNK", 256)),
-                    help="samples per forward chunk (256 = 20 GB of activations; 128 -> 256 is +1.8 %, 512 another +0.4 %)")
+                    help="samples per forward chunk (256 = 20 GB of activations)")
     ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16"])
     ap.add_argument("--cpu-sample", type=int, default=12, help="images in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-config4", action="store_true", help="skip the secondary hybrid 100k record")
+    ap.add_argument("--c4-pool", type=int, default=C4_POOL)
     return ap.parse_args()
 
 
@@ -99,31 +105,21 @@ class ClockSampler:
                 "reasons": reasons, "samples": len(sm)}
 
 
-def golden_model():
-    import numpy as np
-    from oracle.unet_ref import golden_state_dict
-    g = np.load(os.path.join(ROOT, "tests", "golden", "model.npz"))
-    return golden_state_dict(K_CLASSES, g)
+def workload_name(args):
+    return (f"UNet MC-dropout (T={T_REPEATS}) entropy acquisition, FUGC-shape 1x256x256 K={K_CLASSES}, "
+            f"{args.pool}-image synthetic pool (one pool, sharded across the GPUs), budget {BUDGET}")
 
 
-def synthetic_pool_u8(n: int, rank: int):
-    """[n,256,256] uint8 on the CPU: 256 seeded base images (oracle.synth),
-    tiled with per-copy circular shifts so every pool image is distinct."""
-    import torch
-    from oracle.synth import synth_pool_u8
-    base = synth_pool_u8(min(n, 256), start=rank * 1_000_000)
-    reps = (n + base.shape[0] - 1) // base.shape[0]
-    parts = [torch.roll(base, shifts=(7 * r, 13 * r), dims=(1, 2)) for r in range(reps)]
-    return torch.cat(parts)[:n].contiguous()
+def names_hash(names) -> str:
+    return hashlib.sha256("\n".join(map(str, names)).encode()).hexdigest()[:16]
 
 
-# ---------------------------------------------------------------------------
-# CPU reference arm / cpu_baseline
-# ---------------------------------------------------------------------------
+# ---------------------------------------------------------------------------------------------------------------
+# CPU reference arm / cpu_baseline: the oracle port of the reference path (the only place bench.py executes oracle/)
+# ---------------------------------------------------------------------------------------------------------------
 def cpu_pass(sd, images_u8, positions):
-    """One bounded sample of the same workload on the host: composed MC-dropout
-    oracle (reference UNet arithmetic, explicit masks, reference entropy
-    formula) + stable rank."""
+    """One bounded sample of the same workload on the host: composed MC-dropout oracle (reference UNet arithmetic,
+    explicit masks, reference entropy formula) + stable rank."""
     from oracle import select_ref as S
     scores = S.pool_scores_mc(sd, images_u8, positions, T_REPEATS, DROP_P, MC_SEED, "entropy", batch=4)
     return S.rank_desc_stable(scores, min(BUDGET, len(scores)))
@@ -132,9 +128,10 @@ def cpu_pass(sd, images_u8, positions):
 def cpu_baseline(sample: int):
     import numpy as np
     import torch
+    from bench_fixtures import seeded_state_dict, synthetic_pool_u8
     torch.set_num_threads(os.cpu_count())
-    sd = golden_model()
-    imgs = synthetic_pool_u8(sample, 0)
+    sd = seeded_state_dict(K_CLASSES)
+    imgs = synthetic_pool_u8(sample)
     cpu_pass(sd, imgs[:2], np.arange(2))  # warm up thread pools / allocator
     t0 = time.perf_counter()
     cpu_pass(sd, imgs, np.arange(sample))
@@ -150,10 +147,11 @@ def run_reference(args):
         return
     import numpy as np
     import torch
+    from bench_fixtures import seeded_state_dict, synthetic_pool_u8
     torch.set_num_threads(os.cpu_count())
-    sd = golden_model()
+    sd = seeded_state_dict(K_CLASSES)
     per_step = max(2, args.cpu_sample // 3)
-    imgs = synthetic_pool_u8(per_step, 0)
+    imgs = synthetic_pool_u8(per_step)
     for _ in range(min(args.warmup, 1)):
         cpu_pass(sd, imgs[:2], np.arange(2))
     t0 = time.perf_counter()
@@ -162,11 +160,12 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     v = per_step * args.steps / dt
     cb = {"value": v, "unit": "images/s", "cores": os.cpu_count(), "kind": "port",
-          "sample": f"{per_step} images x T={T_REPEATS} per step (oracle port of the reference path, torch fp32 CPU)"}
+          "sample": f"{per_step} images x T={T_REPEATS} per step (oracle port of the reference path, torch fp32 CPU; "
+                    "MC-dropout does not exist in the reference, so the port composes its UNet + Dropout2d + entropy)"}
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args), "note": "CPU host cores; each step is a bounded sample"},
         "cpu_baseline": cb,
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -174,14 +173,13 @@ def run_reference(args):
 
 
 def ncu_traffic():
-    """DRAM bytes per launch (read + write) from the committed `ncu --set full` summaries of the same kernels at the
-    bench's chunk size (profiles/r01_ncu_full_conv_v11.csv: the conv launches of one 128-sample chunk;
-    profiles/r01_ncu_full_uncertainty_v9.csv: 16 images x T=8 per launch).  None when the files are absent."""
+    """DRAM bytes per launch (read + write) from the COMMITTED `ncu --set full` summaries of the same kernels
+    (static: not measured by this run).  conv: mean over the conv launches of one 128-sample chunk; uncertainty: per
+    image.  None when the files are absent."""
     import csv
-    here = os.path.dirname(os.path.abspath(__file__))
 
     def rows(name):
-        path = os.path.join(here, "profiles", name)
+        path = os.path.join(ROOT, "profiles", name)
         if not os.path.exists(path):
             return []
         with open(path) as f:
@@ -195,27 +193,25 @@ def ncu_traffic():
                 out += float(v) * {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}[unit]
         return out
 
-    conv = [total(r) for r in rows("r01_ncu_full_conv_v11.csv")]
-    unc = [total(r) for r in rows("r01_ncu_full_uncertainty_v9.csv")]
-    return (sum(conv) / len(conv) if conv else None), (sum(unc) / len(unc) / 16 if unc else None)
+    conv_file = next((f for f in ("r02_ncu_full_conv.csv", "r01_ncu_full_conv_v11.csv") if rows(f)), None)
+    unc_file, unc_imgs = next(((f, n) for f, n in (("r02_ncu_full_uncertainty_128.csv", 128),
+                                                   ("r01_ncu_full_uncertainty_v9.csv", 16)) if rows(f)), (None, 1))
+    conv = [total(r) for r in rows(conv_file)] if conv_file else []
+    unc = [total(r) for r in rows(unc_file)] if unc_file else []
+    return ((sum(conv) / len(conv) if conv else None), conv_file,
+            (sum(unc) / len(unc) / unc_imgs if unc else None), unc_file)
 
 
-def workload_name(args):
-    return (f"UNet MC-dropout (T={T_REPEATS}) entropy acquisition, FUGC-shape 1x256x256 K={K_CLASSES}, "
-            f"{args.pool}-image synthetic pool per GPU, budget {BUDGET}")
-
-
-# ---------------------------------------------------------------------------
+# ---------------------------------------------------------------------------------------------------------------
 # our arm
-# ---------------------------------------------------------------------------
+# ---------------------------------------------------------------------------------------------------------------
 def run_b200(args):
     import torch
     import torch.distributed as dist
 
     import b200al
-    from b200al import dist as D
-    from oracle.synth import MirrorActive, MirrorExtendable, SynthBase, case_name
-    from oracle.unet_ref import OracleUNet
+    from b200al import selectors as SM
+    from bench_fixtures import StateDictModel, make_active, seeded_state_dict, synthetic_pool_u8
 
     world = int(os.environ.get("WORLD_SIZE", 1))
     rank = int(os.environ.get("RANK", 0))
@@ -225,41 +221,24 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     n = args.pool
-    sd = golden_model()
-    model = OracleUNet(sd)
-    pool_cpu = synthetic_pool_u8(n, rank).pin_memory()
-    pool_dev = pool_cpu.to(dev)
+    model = StateDictModel(seeded_state_dict(K_CLASSES), dropout_p=DROP_P)
 
-    eng = b200al.Engine(dev, K_CLASSES, max_samples=args.chunk, precision=args.precision)
-    eng.load_model(model)
-    lo = rank * n  # global positions of this rank's shard (weak scaling: shards are disjoint pools)
-
-    def step_resident():
-        # MC-dropout masks are keyed by the position inside the rank's own pool (as in the selector path below)
-        scores = eng.scores(pool_dev, "entropy", T=T_REPEATS, drop_p=DROP_P, seed=MC_SEED, base_pos=0)
-        vals, pos = eng.topk(scores, BUDGET, base_pos=lo)
-        if world > 1:
-            vals, pos = D.global_topk(vals, pos, BUDGET)
-        return pos
-
-    # e2e: the public selector API over a host-resident pool (this rank's shard is its whole pool)
-    names = [case_name(lo + i) for i in range(n)] + ["labeled-0"]
-    base = SynthBase(torch.cat([pool_cpu, pool_cpu[:1]]), names)
-    base.images_u8 = base.images_u8.pin_memory()
-    ad = MirrorActive(MirrorExtendable(base, names[n:]), MirrorExtendable(base, names[:n]))
+    # ONE pool (every rank builds the same one): image 0 is the labeled set, images 1..n the pool.
+    # The selector shards pool positions by contiguous ranges (b200al.dist.shard_range) and reads only its shard.
+    host = synthetic_pool_u8(n + 1).pin_memory()
+    ad_resident = make_active(host.to(dev), 1)
+    ad_host = make_active(host, 1)
+    lo, hi = b200al.dist.shard_range(n, rank, world)
     sel = b200al.B200MCDropoutEntropySelector(batch_size=args.chunk, num_workers=0, pin_memory=True,
                                               mc_repeats=T_REPEATS, dropout_prob=DROP_P, mc_seed=MC_SEED,
                                               precision=args.precision, chunk_samples=args.chunk)
-    sel_engine = {}
+    eng = SM.get_engine(dev, K_CLASSES, 256, 256, args.precision, args.chunk)  # the engine the selectors will use
+
+    def step_resident():
+        return sel.select_next_batch(ad_resident, BUDGET, model, dev)
 
     def step_e2e():
-        # single-process semantics per rank (each rank's pool is its own); merge candidates afterwards
-        e, scores, _lo, _hi = _scores_whole_pool(sel, ad, model, dev)
-        sel_engine["e"] = e
-        vals, pos = e.topk(scores, BUDGET, base_pos=lo)
-        if world > 1:
-            vals, pos = D.global_topk(vals, pos, BUDGET)
-        return pos.cpu()  # D2H read of the result
+        return sel.select_next_batch(ad_host, BUDGET, model, dev)
 
     def barrier():
         if world > 1:
@@ -292,10 +271,19 @@ def run_b200(args):
     eng.set_timing(False)
     clocks = sampler.stop() if sampler else None
     launches = eng.kernel_launches() - launches0
+    if world > 1:
+        t = torch.tensor([float(launches)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t)
+        launches = int(t.item())
 
-    step_e2e()  # warm the selector's engine / pinned staging
-    ms_e2e, picked_e2e = timed(step_e2e, max(1, min(args.steps, 2)))
-    e2e_steps = max(1, min(args.steps, 2))
+    e2e_steps = 5 if args.steps >= 5 else max(1, args.steps)
+    step_e2e()  # warm the pinned staging path
+    ms_e2e, picked_e2e = timed(step_e2e, e2e_steps)
+
+    # secondary record: BASELINE config 4 (hybrid entropy -> k-center, 100k pool, budget 500) through the public API
+    c4 = None
+    if not args.no_config4:
+        c4 = run_config4(args, dev, rank, world, timed)
 
     # kernel 3 of the north star on its own: softmax + entropy + mean over fp32 logits resident in HBM
     # (805 MB per launch, larger than L2); algorithmic bytes = T*K*H*W*4 + 4 per image
@@ -317,32 +305,37 @@ def run_b200(args):
         unc = (unc_bytes / (unc_ms / 1e3) / 1e9, unc_ms, unc_bytes)
         del lg
 
-    same = sorted(picked.cpu().tolist()) == sorted(picked_e2e.tolist())
     if rank == 0:
         tf_peak, hbm_peak, peak_src = peaks()
-        value = world * n * args.steps / (ms / 1e3)
+        value = n * args.steps / (ms / 1e3)
         achieved = conv_fl / (conv_ms / 1e3) / 1e12 if conv_ms > 0 else 0.0
-        conv_traffic, unc_traffic_per_image = ncu_traffic()
+        conv_traffic, conv_file, unc_traffic_per_image, unc_file = ncu_traffic()
         line = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "bf16x3 (bf16 hi/lo split operands, fp32 accumulate)"
             if args.precision == "bf16x3" else "bf16", "data": "synthetic",
             "config": {"workload": workload_name(args), "chunk_samples": args.chunk,
+                       "api": "B200MCDropoutEntropySelector.select_next_batch (value: pool resident in HBM; e2e: pool in "
+                              "pinned host memory)",
+                       "sharding": f"contiguous position ranges, {hi - lo} images on rank 0",
                        "l2": "inputs larger than L2 (655 MB pool, >5 GB activations per chunk pass)",
-                       "selection_consistent_resident_vs_e2e": same},
-            "e2e": {"value": world * n * e2e_steps / (ms_e2e / 1e3), "unit": "images/s",
-                    "h2d_bytes_per_step": n * 256 * 256, "d2h_bytes_per_step": BUDGET * 8},
+                       "parity": "MC-dropout is a composed oracle: parity unpinned by the reference (SURVEY F6); "
+                                 "checked against it at T=8 on the 1000-image prefix (tests/test_gpu_configs.py)",
+                       "selection_consistent_resident_vs_e2e": list(picked) == list(picked_e2e),
+                       "picked_sha16": names_hash(picked)},
+            "e2e": {"value": n * e2e_steps / (ms_e2e / 1e3), "unit": "images/s", "steps": e2e_steps,
+                    "h2d_bytes_per_step": n * 256 * 256, "d2h_bytes_per_step": BUDGET * 12 * world},
             "gpu_launches": int(launches),
             "clocks": clocks,
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": tf_peak, "unit": "TFLOP/s",
                          "frac": achieved / tf_peak,
                          "traffic": conv_traffic * args.chunk / 128 if conv_traffic else None,
-                         "traffic_note": "mean DRAM read+write bytes per conv launch, ncu --set full of a 128-sample chunk "
-                                         "(profiles/r01_ncu_full_conv_v11.csv) scaled to this run's chunk_samples "
-                                         "(traffic is per sample: activations in, activations out); tensor-bound "
-                                         "kernels, shown for completeness",
-                         "kernel": "conv_fold_kernel + conv_tc_kernel (tcgen05 implicit GEMM, the 21 conv/convT layers)",
+                         "traffic_note": f"static, from profiles/{conv_file}: mean DRAM read+write bytes per conv launch of "
+                                         "an `ncu --set full` capture of a 128-sample chunk, scaled to this run's "
+                                         "chunk_samples (traffic is per sample); not measured by this run",
+                         "kernel": "conv_fold_kernel + conv_tc_kernel (tcgen05 implicit GEMM, the 21 conv/convT layers), "
+                                   "rank 0's launches",
                          "launches_timed": int(conv_n), "avg_launch_ms": conv_ms / max(conv_n, 1),
                          "flops_note": "algorithmic 2*MAC of the fp32 reference conv; bf16x3 issues 3 MMAs per product, "
                                        "so the tensor pipe runs at >= 3x this rate (frac_of_issue_ceiling = achieved / (peak/3))",
@@ -353,13 +346,14 @@ def run_b200(args):
             line["roofline_hbm_kernel"] = {"bound": "hbm", "achieved": unc[0], "peak": hbm_peak, "unit": "GB/s",
                                            "frac": unc[0] / hbm_peak,
                                            "traffic": unc_traffic_per_image * 128 if unc_traffic_per_image else None,
-                                           "traffic_note": "ncu --set full DRAM read+write bytes per image x 128 images "
-                                                           "(profiles/r01_ncu_full_uncertainty_v9.csv); algorithmic = "
-                                                           "bytes_per_launch",
+                                           "traffic_note": f"static, from profiles/{unc_file} (ncu --set full DRAM read+write "
+                                                           "bytes per image x 128 images); algorithmic = bytes_per_launch",
                                            "kernel": "uncertainty_logits_kernel (softmax + entropy + per-image mean, "
                                                      "128 images x T=8 x K=3 fp32 logits)",
                                            "avg_launch_ms": unc[1], "bytes_per_launch": unc[2],
                                            "peak_source": peak_src}
+        if c4:
+            line["config4"] = c4
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(args.cpu_sample)
         print(json.dumps(line))
@@ -367,16 +361,33 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
-def _scores_whole_pool(sel, ad, model, dev):
-    """The selector's scoring pass for this process' pool, ignoring the process
-    group (weak scaling: each rank's active dataset IS its own pool)."""
-    import b200al.selectors as SM
-    saved = SM.D.world
-    SM.D.world = lambda: (0, 1)
-    try:
-        return sel._scores_local(ad, model, dev)
-    finally:
-        SM.D.world = saved
+def run_config4(args, dev, rank, world, timed):
+    """BASELINE.json configs[3]: hybrid uncertainty + coreset over ONE 100k-image FUGC-shape pool (500 labeled, budget
+    500, entropy pre-filter to 10 x budget), pool resident in HBM, sharded by the selector under the process group."""
+    import torch
+
+    import b200al
+    from bench_fixtures import StateDictModel, make_active, seeded_state_dict, synthetic_pool_u8
+    n = args.c4_pool
+    model = StateDictModel(seeded_state_dict(K_CLASSES))
+    images = synthetic_pool_u8(C4_LABELED + n)
+    ad = make_active(images.to(dev), C4_LABELED)
+    del images
+    kw = dict(batch_size=args.chunk, num_workers=0, pin_memory=True, precision=args.precision, chunk_samples=args.chunk)
+    sel = b200al.B200HybridSelector(**kw)
+    picked = sel.select_next_batch(ad, C4_BUDGET, model, dev)   # warm
+    ms, picked = timed(lambda: sel.select_next_batch(ad, C4_BUDGET, model, dev), 2)
+    prof = b200al.B200HybridSelector(profile_stages=True, **kw)
+    prof.select_next_batch(ad, C4_BUDGET, model, dev)
+    stages = {k: round(v, 4) for k, v in prof.last_timing["stages"].items()}
+    del ad
+    torch.cuda.empty_cache()
+    return {"workload": f"hybrid entropy -> k-center (l2), FUGC-shape, {n}-image pool (one pool, sharded), "
+                        f"{C4_LABELED} labeled, budget {C4_BUDGET}, B200HybridSelector.select_next_batch",
+            "seconds": ms / 2 / 1e3, "images_per_s": n / (ms / 2 / 1e3), "steps": 2,
+            "picked_sha16": names_hash(sorted(picked)), "n_picked": len(picked),
+            "stage_seconds_rank0": stages,
+            "stage_note": "separate profiled call (device synchronised at stage boundaries)"}
 
 
 if __name__ == "__main__":

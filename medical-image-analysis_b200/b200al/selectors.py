@@ -150,18 +150,48 @@ class PoolSource:
             off += img.shape[0]
 
 
+class _Stages:
+    """Per-stage wall time of one select_next_batch (weights / score / embed / gather / rank / kcenter ...).  Off by
+    default: with `profile_stages=True` the device is synchronised at every stage boundary, which costs overlap."""
+
+    def __init__(self, enabled: bool, device):
+        self.enabled, self.times = enabled, {}
+        self.device = torch.device(device)
+        self._name, self._t0 = None, 0.0
+
+    def _sync(self):
+        if self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+
+    def start(self, name: str):
+        if not self.enabled:
+            return
+        self.stop()
+        self._sync()
+        self._name, self._t0 = name, time.perf_counter()
+
+    def stop(self):
+        if self.enabled and self._name is not None:
+            self._sync()
+            self.times[self._name] = self.times.get(self._name, 0.0) + time.perf_counter() - self._t0
+            self._name = None
+
+
 def _timed(fn):
     @functools.wraps(fn)
     def wrapper(self, active_dataset, select_num, model, device):
         dev = torch.device(device)
+        self._stages = _Stages(self.profile_stages, dev)
         t0 = time.perf_counter()
         out = fn(self, active_dataset, select_num, model, device)
+        self._stages.stop()
         if dev.type == "cuda":
             torch.cuda.synchronize(dev)
         dt = time.perf_counter() - t0
         labeled, pool = active_dataset.get_size()
         self.last_timing = {"seconds": dt, "pool": pool, "labeled": labeled, "selected": len(out),
-                            "images_per_s": pool / dt if dt > 0 else float("inf")}
+                            "images_per_s": pool / dt if dt > 0 else float("inf"),
+                            "stages": dict(self._stages.times)}
         log.info("%s: %d of %d pool images selected in %.3f s (%.0f images/s, %d labeled)", type(self).__name__,
                  len(out), pool, dt, self.last_timing["images_per_s"], labeled)
         return out
@@ -172,7 +202,7 @@ def _timed(fn):
 class _B200Base(ActiveSelector):
     def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8, *,
                  precision: str = "bf16x3", chunk_samples: int = 64, pool_cache: str = "auto",
-                 sync_weights: bool = True):
+                 sync_weights: bool = True, profile_stages: bool = False):
         self.batch_size, self.num_workers, self.pin_memory = batch_size, num_workers, pin_memory
         self.smooth = smooth
         self.precision = precision
@@ -182,6 +212,8 @@ class _B200Base(ActiveSelector):
         self.pool_cache = pool_cache
         self.sync_weights = bool(sync_weights)  # multi-GPU: every rank scores with rank 0's weights
         self.last_timing: dict | None = None
+        self.profile_stages = bool(profile_stages)
+        self._stages = _Stages(False, "cpu")
 
     def __init_subclass__(cls, **kw):
         super().__init_subclass__(**kw)
@@ -192,6 +224,7 @@ class _B200Base(ActiveSelector):
         return PoolSource(dataset, device, self.batch_size, self.num_workers, self.pin_memory, self.pool_cache)
 
     def _engine(self, model, device, hw) -> Engine:
+        self._stages.start("weights")
         sd = model.state_dict()
         K = validate_state_dict(sd)
         eng = get_engine(device, K, hw[0], hw[1], self.precision, self.chunk_samples)
@@ -231,6 +264,7 @@ class _B200Uncertainty(_B200Base):
         lo, hi = D.shard_range(len(pool), rank, ws)
         src = self._source(pool, device)
         eng = self._engine(model, device, src.image_hw())
+        self._stages.start("score")
         return eng, self._score_positions(eng, src, list(range(lo, hi))), lo, hi
 
     def cal_scores(self, active_dataset, model, device):
@@ -245,6 +279,7 @@ class _B200Uncertainty(_B200Base):
         if labeled_size == 0:
             return _cold_start(active_dataset, select_num)
         eng, scores, lo, _hi = self._scores_local(active_dataset, model, device)
+        self._stages.start("rank")
         vals, pos = eng.topk(scores, select_num, base_pos=lo)
         if D.world()[1] > 1:
             vals, pos = D.global_topk(vals, pos, select_num)
@@ -422,10 +457,14 @@ class B200CoresetSelector(_B200Base):
         psrc = self._source(pool, device)
         lsrc = self._source(labeled, device)
         eng = self._engine(model, device, psrc.image_hw())
+        self._stages.start("embed")
         emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
-        emb_p = D.gather_rows(_embed_positions(eng, psrc, list(range(lo, hi))))
+        emb_local = _embed_positions(eng, psrc, list(range(lo, hi)))
+        self._stages.start("gather")
+        emb_p = D.gather_rows(emb_local)
         feats = torch.cat([emb_l, emb_p], 0)
         _require_finite(feats, "embeddings")
+        self._stages.start("kcenter")
         if self.has_loaded:
             loaded = torch.from_numpy(_loaded_feature_rows(all_list, self.feature_dict, self.feature_path))
             _require_finite(loaded, "loaded features")
@@ -648,17 +687,23 @@ class B200HybridSelector(_B200Uncertainty):
         psrc = self._source(pool, device)
         lsrc = self._source(labeled, device)
         eng = self._engine(model, device, psrc.image_hw())
+        self._stages.start("score")
         scores = self._score_positions(eng, psrc, list(range(lo, hi)))
+        self._stages.start("rank")
         m = min(pool_size, self.prefilter_factor * select_num)
         vals, pos = eng.topk(scores, m, base_pos=lo)
         if ws > 1:
             vals, pos = D.global_topk(vals, pos, m)
         cand = sorted(pos.tolist())  # pool order -> positional tie-break inside k-center
         mine = [p for p in cand if lo <= p < hi]
-        emb_c = D.gather_rows(_embed_positions(eng, psrc, mine))
+        self._stages.start("embed")
+        emb_mine = _embed_positions(eng, psrc, mine)
         emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
+        self._stages.start("gather")
+        emb_c = D.gather_rows(emb_mine)
         feats = torch.cat([emb_l, emb_c], 0)
         _require_finite(feats, "embeddings")
+        self._stages.start("kcenter")
         picks = _check_picks(eng.kcenter(feats, labeled_size, select_num, "l2").tolist(), "k-center")
         return [pool.image_idx[cand[i - labeled_size]] for i in picks]
 

@@ -292,11 +292,12 @@ def stage_select():
 
 
 def merge():
-    out = {"versions": np.array(repr(versions()))}
+    path = os.path.join(OUT, "configs.npz")
+    out = dict(np.load(path)) if os.path.exists(path) else {}   # stages frozen by earlier runs stay
+    out["versions"] = np.array(repr(versions()))
     for f in ("c1.npz", "c2.npz", "select.npz"):
         if os.path.exists(tmp(f)):
             out.update(np.load(tmp(f)))
-    path = os.path.join(OUT, "configs.npz")
     np.savez_compressed(path, **out)
     log("wrote", path, os.path.getsize(path), "bytes:", sorted(out))
 

@@ -69,9 +69,11 @@ def test_uncertainty_selectors_pick_reference_set(env, K, name):
     ad = make_active(e["images"], e["L"])
     got = sel.select_next_batch(ad, e["k"], e["model"], torch.device(DEV))
     want = e["g"][f"selected/{name}"].tolist()
-    # the golden cut is not a near-tie: gap >> score tolerance
+    # the golden cut is not a near-tie: its gap is at least 10x the error the GPU scores actually show
     sc = e["g"][f"scores/{name}"]
-    assert S.boundary_gap(sc, e["k"]) > 10 * SCORE_RTOL * np.abs(sc).max() * 0.1
+    gpu_scores, _ = sel.cal_scores(make_active(e["images"], e["L"]), e["model"], torch.device(DEV))
+    err = np.abs(gpu_scores.cpu().numpy() - sc).max()
+    assert S.boundary_gap(sc, e["k"]) > 10 * err, (S.boundary_gap(sc, e["k"]), err)
     assert got == want            # same names, same order (descending score)
     assert len(set(got)) == len(got) and all(n in ad.get_pool_dataset().image_idx for n in got)
     ad.extend_train_set(got)      # what the trainer does next (active_dataset.py:41-44)
@@ -119,7 +121,8 @@ def test_coreset_selector_end_to_end(env, K, metric):
     _p, gaps = S.kcenter_greedy_stream(e["g"]["embeddings"], e["L"], e["k"], metric, return_gaps=True)
     bound = 2 * np.sqrt(512) * 1e-4 * np.abs(e["g"]["embeddings"]).max()
     assert min(gaps) < bound, f"picked a different set although the golden run has no near-tie (min gap {min(gaps):.2e})"
-    pytest.skip(f"golden k-center run has a near-tie (min top-2 gap {min(gaps):.2e} < {bound:.2e})")
+    pytest.xfail(f"golden k-center run has a near-tie (min top-2 gap {min(gaps):.2e} < {bound:.2e}): a different set "
+                 "is within the stated embedding tolerance, reported as an expected failure, not hidden as a skip")
 
 
 def test_kcenter_random_features_exact():
