@@ -106,10 +106,12 @@ def test_kmean_selector_contract_and_registry():
     import b200al
     with pytest.raises(NotImplementedError):
         b200al.B200KMeanSelector(batch_size=1, num_workers=0, metric="l1")
-    with pytest.raises(NotImplementedError):
-        b200al.B200KMeanSelector(batch_size=1, num_workers=0, feature_path="/tmp/x")
-    with pytest.raises(NotImplementedError):  # mixing model and loaded features: result dtype depends on the numpy version
-        b200al.B200KMeanSelector(batch_size=1, num_workers=0, feature_dict={"a": [1.0, 2.0]})
+    # round 2: feature_path (.h5 / .npy / .npz per case) and the model + loaded mix are supported
+    # (tests/test_gpu_round2.py); what stays refused is loaded_feature_only without any loaded features
+    assert str(b200al.B200KMeanSelector(batch_size=1, num_workers=0, feature_path="/tmp/x").feature_path) == "/tmp/x"
+    assert b200al.B200KMeanSelector(batch_size=1, num_workers=0, feature_dict={"a": [1.0, 2.0]}).has_loaded
+    with pytest.raises(ValueError):
+        b200al.B200KMeanSelector(batch_size=1, num_workers=0, loaded_feature_only=True)
     with pytest.raises(RuntimeError):
         b200al.B200KMeanSelector(batch_size=1, num_workers=0, coreset_criteria="median")
     s = b200al.SELECTORS["b200-kmean-l2"](batch_size=2, num_workers=0, pin_memory=False)

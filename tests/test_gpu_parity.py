@@ -337,5 +337,5 @@ def test_kcenter_fused_add_matches_oracle_and_reference_golden(golden):
     cold = b200al.B200CoresetSelector(metric="l2", **kw).select_next_batch(make_active(images, 0), BUDGET, model,
                                                                           torch.device(DEV))
     assert cold == gf["selected/cold"].tolist()
-    with pytest.raises(NotImplementedError):
-        b200al.B200CoresetSelector(batch_size=1, num_workers=0, feature_dict=fd, coreset_fusion="cat")
+    with pytest.raises(NotImplementedError):   # "cat" is built since round 2 (tests/test_gpu_round2.py); anything else is not
+        b200al.B200CoresetSelector(batch_size=1, num_workers=0, feature_dict=fd, coreset_fusion="mul")
