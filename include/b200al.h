@@ -182,6 +182,21 @@ int b200al_kmeans_pp(b200al_ctx* ctx, const float* d_X, int n, int D, const floa
                      void* stream);
 int b200al_normalize_rows(b200al_ctx* ctx, const float* d_in, float* d_out, int n, int D, void* stream);
 
+/* Rank & cut WITHOUT any allocation - no counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  Same result as b200al_topk (k best of n scores, descending, ties -> lower position first), but it needs no
+ * context and its scratch (64-bit keys, candidates, radix state) lives in a file-scope `static __device__` array of
+ * the library, sized for n <= B200AL_TOPK_STATIC_MAX_N scores (4 MiB + 1 KiB, held by every GPU that loads the
+ * library until the process exits).  n beyond that is rejected with B200AL_ERR_ARG.  `device` is made current; the
+ * first call on a device resolves the array's device address (cudaGetSymbolAddress) - make that call outside a
+ * graph capture.  No cudaMalloc / cudaFree / allocating library routine is called, ever.
+ * ALL calls on one GPU share the one array: it keeps the previous call's contents (everything that must start at
+ * zero is cleared by the call itself), and two calls that overlap on the GPU (different streams, or different host
+ * threads) race - serialise them.  Asynchronous on `stream`. */
+#define B200AL_TOPK_STATIC_MAX_N 262144
+int b200al_topk_static(int device, const float* d_scores, int n, int k, int64_t base_pos, float* d_out_scores,
+                       int64_t* d_out_pos, void* stream);
+
 /* Introspection for benches / tests. */
 int b200al_kernel_launches(const b200al_ctx* ctx, int64_t* out_count);      /* kernels launched so far */
 /* CUDA-event timing around every tcgen05 conv launch (up to 32768 launches

@@ -16,6 +16,7 @@ NUM_BLOCKS = 18
 NUM_UPSAMPLES = 4
 MASK_CHANNELS = 2944
 EMBED_DIM = 512
+TOPK_STATIC_MAX_N = 262144  # B200AL_TOPK_STATIC_MAX_N
 
 ENTROPY, MARGIN, CONFIDENCE, DICE = 0, 1, 2, 3
 L2, COSINE = 0, 1
@@ -68,6 +69,7 @@ PROTOTYPES = {
     "b200al_uncertainty_from_logits": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                                  C.c_float, C.c_void_p, C.c_void_p]),
     "b200al_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200al_topk_static": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200al_kcenter_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,
                                       C.c_void_p, C.c_int, C.c_void_p]),
     "b200al_kcenter_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,

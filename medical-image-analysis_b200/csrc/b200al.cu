@@ -1125,6 +1125,81 @@ extern "C" int b200al_topk(b200al_ctx* ctx, const float* d_scores, int n, int k,
 }
 
 // ---------------------------------------------------------------------------
+// rank & cut without allocation (include/b200al.h: b200al_topk_static)
+// ---------------------------------------------------------------------------
+namespace {
+// layout: keys [MAX_N] u64 | candidates [MAX_N] u64 | TopkState
+constexpr size_t kTopkStaticKeysBytes = (size_t)B200AL_TOPK_STATIC_MAX_N * sizeof(unsigned long long);
+constexpr size_t kTopkStaticBytes = 2 * kTopkStaticKeysBytes + ((sizeof(TopkState) + 255) / 256) * 256;
+}  // namespace
+// File scope, not in a namespace: in HOST code this name is only a stand-in for the symbol (its host address is not a
+// device address); the device address is resolved per device with cudaGetSymbolAddress below.
+static __device__ __align__(256) unsigned char g_topk_static_scratch[kTopkStaticBytes];
+
+namespace {
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+void* g_static_ptr[kMaxDevices] = {nullptr};  // device address of g_topk_static_scratch on device i
+int g_static_sms[kMaxDevices] = {0};
+
+// once per device, with that device current
+int topk_static_setup(int device, void** scratch, int* sms) {
+  std::lock_guard<std::mutex> lk(g_static_mu);
+  if (!g_static_ptr[device]) {
+    void* ptr = nullptr;
+    cudaError_t e = cudaGetSymbolAddress(&ptr, g_topk_static_scratch);
+    if (e != cudaSuccess || !ptr)
+      return set_err(nullptr, B200AL_ERR_CUDA, "cudaGetSymbolAddress(topk static scratch) on device %d: %s", device,
+                     cudaGetErrorString(e));
+    int n_sm = 0;
+    e = cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, device);
+    if (e != cudaSuccess || n_sm < 1)
+      return set_err(nullptr, B200AL_ERR_CUDA, "cudaDeviceGetAttribute(SM count) on device %d: %s", device,
+                     cudaGetErrorString(e));
+    g_static_sms[device] = n_sm;
+    g_static_ptr[device] = ptr;
+  }
+  *scratch = g_static_ptr[device];
+  *sms = g_static_sms[device];
+  return 0;
+}
+}  // namespace
+
+extern "C" int b200al_topk_static(int device, const float* d_scores, int n, int k, int64_t base_pos,
+                                  float* d_out_scores, int64_t* d_out_pos, void* stream) {
+  if (n < 0 || k < 0) return set_err(nullptr, B200AL_ERR_ARG, "negative size");
+  if (n > B200AL_TOPK_STATIC_MAX_N)
+    return set_err(nullptr, B200AL_ERR_ARG,
+                   "b200al_topk_static: n = %d exceeds the static scratch (B200AL_TOPK_STATIC_MAX_N = %d); use "
+                   "b200al_topk", n, B200AL_TOPK_STATIC_MAX_N);
+  if (device < 0 || device >= kMaxDevices) return set_err(nullptr, B200AL_ERR_ARG, "device %d out of range", device);
+  if (k > n) k = n;
+  if (k == 0) return B200AL_OK;
+  if (!d_scores || !d_out_scores || !d_out_pos) return set_err(nullptr, B200AL_ERR_ARG, "NULL pointer");
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(nullptr, cudaSetDevice(device));
+  void* scratch = nullptr;
+  int sms = 0;
+  if (int rc = topk_static_setup(device, &scratch, &sms)) return rc;
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(scratch);
+  unsigned long long* cand = keys + B200AL_TOPK_STATIC_MAX_N;
+  TopkState* state = reinterpret_cast<TopkState*>(reinterpret_cast<unsigned char*>(scratch) + 2 * kTopkStaticKeysBytes);
+  // same launches as b200al_topk; topk_keys_kernel resets the state (prefix, remaining, count, histogram) and every
+  // key / candidate slot that is read is written first, so the previous call's contents never matter
+  const int blocks = (n + 255) / 256 < sms * 8 ? (n + 255) / 256 : sms * 8;
+  topk_keys_kernel<<<blocks, 256, 0, st>>>(d_scores, n, keys, state, (unsigned)k);
+  for (int pass = 0; pass < 8; ++pass) {
+    topk_hist_kernel<<<blocks, 256, 0, st>>>(keys, n, state, pass);
+    topk_scan_kernel<<<1, 32, 0, st>>>(state, pass);
+  }
+  topk_compact_kernel<<<blocks, 256, 0, st>>>(keys, n, state, cand, (unsigned)k);
+  topk_rank_kernel<<<(k + 255) / 256, 256, 0, st>>>(cand, (unsigned)k, (long long)base_pos, d_out_scores,
+                                                   (long long*)d_out_pos);
+  CUDA_TRY(nullptr, cudaGetLastError());
+  return B200AL_OK;
+}
+
+// ---------------------------------------------------------------------------
 // k-center greedy
 // ---------------------------------------------------------------------------
 namespace {
