@@ -53,7 +53,7 @@ def parse():
     ap.add_argument("--pool", type=int, default=POOL, help="images in the (one, sharded) pool")
     ap.add_argument("--chunk", type=int, default=int(os.environ.get("B200AL_CHUNK", 256)),
                     help="samples per forward chunk (256 = 20 GB of activations)")
-    ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16"])
+    ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16", "mixed", "mixed-deep"])
     ap.add_argument("--cpu-sample", type=int, default=12, help="images in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-config4", action="store_true", help="skip the secondary hybrid 100k record")
@@ -103,6 +103,26 @@ class ClockSampler:
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower() == "active" for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
+
+
+DTYPES = {
+    "bf16x3": "bf16x3 (bf16 hi/lo split operands, 3 MMAs per product, fp32 accumulate)",
+    "bf16": "bf16",
+    "mixed": "per-layer mix, fp32 accumulate: fp16 single operands (1 MMA) in encoder.levels.2.1 ... decoder.upsamples.2 "
+             "(12 layers, <= 64x64), bf16x3 in the other 9 tensor-core layers, fp32 first conv / head",
+    "mixed-deep": "per-layer mix, fp32 accumulate: fp16 single operands (1 MMA) in encoder.levels.3.1 ... "
+                  "decoder.upsamples.1 (7 layers, <= 32x32), bf16x3 in the other 14 tensor-core layers",
+}
+
+
+def issue_factor(precision: str) -> float:
+    """MMAs issued per algorithmic MAC, FLOP-weighted over the 21 tensor-core layers (SURVEY 8a' per-layer GFLOP)."""
+    if precision == "bf16":
+        return 1.0
+    gf = [1.208, 0.604, 1.208, 0.604, 1.208, 0.604, 1.208, 0.604, 1.208, 0.268, 2.416, 1.208, 0.268, 2.416, 1.208,
+          0.268, 2.416, 1.208, 0.268, 2.416, 1.208]   # library layer order (first conv excluded)
+    group = {"bf16x3": range(0), "mixed": range(4, 16), "mixed-deep": range(6, 13)}[precision]
+    return sum(g * (1 if i in group else 3) for i, g in enumerate(gf)) / sum(gf)
 
 
 def workload_name(args):
@@ -313,8 +333,7 @@ def run_b200(args):
         line = {
             "metric": METRIC, "value": value, "unit": "images/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "bf16x3 (bf16 hi/lo split operands, fp32 accumulate)"
-            if args.precision == "bf16x3" else "bf16", "data": "synthetic",
+            "vs_baseline": None, "dtype": DTYPES[args.precision], "data": "synthetic",
             "config": {"workload": workload_name(args), "chunk_samples": args.chunk,
                        "api": "B200MCDropoutEntropySelector.select_next_batch (value: pool resident in HBM; e2e: pool in "
                               "pinned host memory)",
@@ -339,7 +358,7 @@ def run_b200(args):
                          "launches_timed": int(conv_n), "avg_launch_ms": conv_ms / max(conv_n, 1),
                          "flops_note": "algorithmic 2*MAC of the fp32 reference conv; bf16x3 issues 3 MMAs per product, "
                                        "so the tensor pipe runs at >= 3x this rate (frac_of_issue_ceiling = achieved / (peak/3))",
-                         "frac_of_issue_ceiling": (achieved * (3 if args.precision == "bf16x3" else 1)) / tf_peak,
+                         "frac_of_issue_ceiling": achieved * issue_factor(args.precision) / tf_peak,
                          "peak_source": peak_src},
         }
         if unc:

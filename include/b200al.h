@@ -49,7 +49,14 @@ enum b200al_metric { B200AL_L2 = 0, B200AL_COSINE = 1 }; /* CoresetSelector(metr
 enum b200al_criteria { B200AL_MIN = 0, B200AL_MEAN = 1 }; /* CoresetSelector(coreset_criteria=...) */
 enum b200al_precision {
   B200AL_BF16X3 = 0, /* bf16 hi/lo split operands, 3 MMAs per k-step, fp32 accumulate (default; parity grade) */
-  B200AL_BF16 = 1    /* single bf16 operands (fast; does not meet the 2e-2 logit tolerance) */
+  B200AL_BF16 = 1,   /* single bf16 operands (fast; does not meet the 2e-2 logit tolerance) */
+  /* Per-layer mix for the SCORING path (b200al_unet_scores): the deep layers - encoder.levels.2.1 ... decoder.upsamples.2,
+   * 64x64 resolution and below - contract single fp16 operands (one MMA per product, one activation plane), everything
+   * else stays bf16x3.  Emulated on the golden probes (tools/precision_table.py, profiles/r02_precision.json): 7e-3 max
+   * logit error, 8e-6 relative score error against the fp32 reference (tolerances 2e-2 / 1e-3).  Embeddings
+   * (b200al_unet_embed), BADGE and the test hooks run bf16x3 throughout in this mode. */
+  B200AL_MIXED = 2,
+  B200AL_MIXED_DEEP = 3 /* the same with the smaller group encoder.levels.3.1 ... decoder.upsamples.1 (2.5e-3 / 3e-6) */
 };
 enum b200al_image_dtype { B200AL_U8 = 0 /* x/255, torchvision to_tensor */, B200AL_F32 = 1 };
 

@@ -20,14 +20,14 @@ TOPK_STATIC_MAX_N = 262144  # B200AL_TOPK_STATIC_MAX_N
 
 ENTROPY, MARGIN, CONFIDENCE, DICE = 0, 1, 2, 3
 L2, COSINE = 0, 1
-BF16X3, BF16 = 0, 1
+BF16X3, BF16, MIXED, MIXED_DEEP = 0, 1, 2, 3
 U8, F32 = 0, 1
 
 MODES = {"entropy": ENTROPY, "margin": MARGIN, "confidence": CONFIDENCE, "dice": DICE}
 METRICS = {"l2": L2, "cosine": COSINE}
 CRIT_MIN, CRIT_MEAN = 0, 1
 CRITERIA = {"min": CRIT_MIN, "mean": CRIT_MEAN}
-PRECISIONS = {"bf16x3": BF16X3, "bf16": BF16}
+PRECISIONS = {"bf16x3": BF16X3, "bf16": BF16, "mixed": MIXED, "mixed-deep": MIXED_DEEP}
 
 
 class BlockWeights(C.Structure):

@@ -69,6 +69,11 @@ struct Layer {
   ConvFoldParams fp;
   int slots = 0;
   double flops_per_sample = 0;
+  int index = 0;        // position in forward order (timing records)
+  // mixed-precision scoring path (conv_tc.cuh FMT): nsplit 0 = the context's; fmt 1 = fp16 single-plane output,
+  // 2 = fp16 single-plane operands and output, 3 = fp16 operands, bf16 hi/lo output
+  int nsplit = 0, fmt = 0;
+  __half* wp16 = nullptr;  // packed single-plane fp16 weights [tap][N][Cin] (fmt >= 2)
 };
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -85,6 +90,11 @@ struct b200al_ctx {
   EncodeTiledFn encode = nullptr;
   ActBuf bufs[NUM_BUFS];
   std::vector<Layer> layers;  // 21 tensor-core layers in forward order (first conv and head are separate)
+  // B200AL_MIXED: the same 21 layers as the SCORING path runs them - layers [mix_first, mix_last] contract single
+  // fp16 operands, layer mix_first - 1 already stores fp16 for them, mix_last stores a bf16 pair again.  The
+  // embedding / BADGE / test paths keep using `layers` (bf16x3 throughout).
+  std::vector<Layer> mix_layers;
+  int mix_first = -1, mix_last = -1;
   // first conv + head
   float *first_w = nullptr, *first_bias = nullptr, *first_scale = nullptr, *first_shift = nullptr;
   FirstConvConsts first_consts;  // host copy of the folded first-conv constants (passed as a kernel parameter)
@@ -294,10 +304,17 @@ ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw, bool pair = false, 
 int stage_bytes(int bn, int bk, int nsplit, bool pair = false, int mt = 1) {
   return (nsplit == 3 ? 2 : 1) * (mt * 128 * bk * 2 + (pair ? bn / 2 : bn) * bk * 2);
 }
-int out_buf_bytes(int cw, int nsplit) { return (nsplit == 3 ? 2 : 1) * 128 * cw * 2; }
-int conv_smem_bytes(int bn, int bk, int nsplit, int stages, int cw, int nbufs_total, bool pair = false, int mt = 1) {
-  return stages * stage_bytes(bn, bk, nsplit, pair, mt) + nbufs_total * out_buf_bytes(cw, nsplit) + 1024 + 8 * bn * 4;
+int out_buf_bytes(int cw, int oplanes) { return oplanes * 128 * cw * 2; }
+int conv_smem_bytes(int bn, int bk, int nsplit, int oplanes, int stages, int cw, int nbufs_total, bool pair = false,
+                    int mt = 1) {
+  return stages * stage_bytes(bn, bk, nsplit, pair, mt) + nbufs_total * out_buf_bytes(cw, oplanes) + 1024 + 8 * bn * 4;
 }
+// per-layer operand split and number of output planes (conv_tc.cuh FMT)
+int layer_nsplit(const b200al_ctx* ctx, const Layer& L);
+int layer_oplanes(const b200al_ctx* ctx, const Layer& L);
+ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt);
+ConvKernelFn layer_kernel(const b200al_ctx* ctx, const Layer& L);
+int layer_smem(const b200al_ctx* ctx, const Layer& L);
 
 typedef void (*FoldKernelFn)(const CUtensorMap, const CUtensorMap, const CUtensorMap, const ConvFoldParams, const int);
 FoldKernelFn pick_fold_kernel(int cin, int nsplit, int headk = 0) {
@@ -357,7 +374,8 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
     if (L.bn != 128 && L.bn != 256) L.pair = false, L.bn = n_total < bn_max ? n_total : bn_max;
   }
   // smem policy: small tiles aim for 2 CTAs/SM (<= ~110 KB each), large ones take the whole SM.
-  const int sb = stage_bytes(L.bn, L.bk, ctx->nsplit, L.pair);
+  const int ns = layer_nsplit(ctx, L), opl = layer_oplanes(ctx, L);
+  const int sb = stage_bytes(L.bn, L.bk, ns, L.pair);
   const int kMaxSmem = 227 * 1024;
   const int fixed = 1024 + 8 * L.bn * 4;
   L.cw = (L.bn >= 64 && L.cout >= 64) ? 64 : 32;
@@ -369,14 +387,14 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   L.ngroups = env_int("B200AL_NGROUPS", num_kb <= 18 ? 2 : 1);
   L.nbuf = L.ngroups == 2 ? 1 : 2;
   const int budget2 = env_int("B200AL_SMEM_BUDGET", 110 * 1024);
-  int st = L.pair ? 0 : (budget2 - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
+  int st = L.pair ? 0 : (budget2 - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, opl)) / sb;
   if (st < 3) {  // one CTA per SM
-    st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
+    st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, opl)) / sb;
     if (st < 3 && L.ngroups * L.nbuf > 1) {
       if (L.ngroups == 1) L.nbuf = 1;
-      st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, ctx->nsplit)) / sb;
+      st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(L.cw, opl)) / sb;
     }
-    if (st < 3 && L.cw == 64) { L.cw = 32; st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(32, ctx->nsplit)) / sb; }
+    if (st < 3 && L.cw == 64) { L.cw = 32; st = (kMaxSmem - fixed - L.ngroups * L.nbuf * out_buf_bytes(32, opl)) / sb; }
   }
   if (st > 8) st = 8;
   if (st < 2) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "conv tile does not fit shared memory");
@@ -394,9 +412,9 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
     int bk2 = L.bk;
     if (L.bn == 128) bk2 = 32;  // 2 x 128 x 64-channel tiles + a 128-row weight tile leave room for one stage only
     if (L.bn == 64 && env_int("B200AL_MT2_BK", 64) == 32) bk2 = 32;
-    const int sb2 = stage_bytes(L.bn, bk2, ctx->nsplit, false, 2);
-    const int st2 = (kMaxSmem - fixed - 2 * out_buf_bytes(32, ctx->nsplit)) / sb2;
-    if (st2 >= 2 && pick_kernel(L.bn, bk2, ctx->nsplit, 32, false, 2)) {
+    const int sb2 = stage_bytes(L.bn, bk2, ns, false, 2);
+    const int st2 = (kMaxSmem - fixed - 2 * out_buf_bytes(32, opl)) / sb2;
+    if (st2 >= 2 && (L.fmt ? pick_kernel_fmt(L.bn, bk2, 32, false, 2, L.fmt) : pick_kernel(L.bn, bk2, ns, 32, false, 2))) {
       L.mt = 2; L.bk = bk2; L.cw = 32; L.ngroups = 2; L.nbuf = 1;
       L.stages = st2 > 8 ? 8 : st2;
     }
@@ -428,7 +446,7 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
     }
   }
   // Cout = 64 runs as two launches of 32 output channels each (the resident weights of one half fit, all 64 do not)
-  L.fold = L.kind == KIND_CONV3 && L.stride == 1 && outH % 4 == 0 && env_int("B200AL_FOLD", 1) != 0 &&
+  L.fold = L.fmt == 0 && L.kind == KIND_CONV3 && L.stride == 1 && outH % 4 == 0 && env_int("B200AL_FOLD", 1) != 0 &&
            ((L.cin == 32 && L.cout == 32 && ib.c_total == 32 && L.in.c_off == 0) ||
             (L.cin == 64 && (L.cout == 32 || (L.cout == 64 && env_int("B200AL_FOLD64", 1)))));
   if (L.fold) {
@@ -459,7 +477,7 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   p.out_H = outH;
   p.shuffle = L.kind == KIND_CONVT;
   p.cout = L.cout;
-  p.write_lo = ctx->nsplit == 3;
+  p.write_lo = opl == 2;
   p.mask_stride = B200AL_MASK_CHANNELS;
   const double px = L.kind == KIND_CONV3 ? (double)outH * outW : (double)inH * inW;
   L.flops_per_sample = 2.0 * px * n_total * (double)(p.taps * L.cin);
@@ -499,7 +517,7 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
     dim3 fgrid((unsigned)(f.total_tiles < ctx->sm_count ? f.total_tiles : ctx->sm_count));
     const int fsmem = fold_smem_bytes(L.cin, ctx->nsplit, L.slots);
     const bool ft = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
-    if (ft) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
+    if (ft) { ctx->ev_layer[ctx->ev_used / 2] = L.index; cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
     f.w_cout_total = L.cout;
     for (int co0 = 0; co0 < L.cout; co0 += 32) {
       ConvFoldParams g = f;
@@ -515,8 +533,8 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
     CUDA_TRY(ctx, cudaGetLastError());
     return 0;
   }
-  ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw, L.pair, L.mt);
-  if (!fn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no conv kernel for BN=%d BK=%d", L.bn, L.bk);
+  ConvKernelFn fn = layer_kernel(ctx, L);
+  if (!fn) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no conv kernel for BN=%d BK=%d fmt=%d", L.bn, L.bk, L.fmt);
   ConvTcParams q = p;
   q.n_tiles = p.n_total / L.bn;
   q.total_tiles = S * p.tiles_x * p.tiles_y * q.n_tiles;
@@ -530,9 +548,9 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
   const int work = L.mt == 2 ? q.total_tiles / 2 : q.total_tiles;
   unsigned nblk = (unsigned)(work < resident ? work : resident);
   if (q.cluster) nblk &= ~1u;
-  const int smem = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups, L.pair, L.mt);
+  const int smem = layer_smem(ctx, L);
   const bool t = ctx->timing && ctx->ev_used + 2 <= ctx->ev.size();
-  if (t) { ctx->ev_layer[ctx->ev_used / 2] = (int)(&L - ctx->layers.data()); cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
+  if (t) { ctx->ev_layer[ctx->ev_used / 2] = L.index; cudaEventRecord(ctx->ev[ctx->ev_used++], st); ctx->conv_flops += L.flops_per_sample * S; ctx->conv_timed++; }
   {
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(nblk);
@@ -558,6 +576,42 @@ int launch_conv(b200al_ctx* ctx, Layer& L, const CUtensorMap& tmA, const CUtenso
 
 }  // namespace
 
+namespace {
+int layer_nsplit(const b200al_ctx* ctx, const Layer& L) { return L.nsplit ? L.nsplit : ctx->nsplit; }
+int layer_oplanes(const b200al_ctx* ctx, const Layer& L) {
+  if (L.fmt == 0) return layer_nsplit(ctx, L) == 3 ? 2 : 1;
+  return L.fmt == 3 ? 2 : 1;
+}
+// The format variants are instantiated for the tile shapes the planner gives the layers of the fp16 groups only.
+ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt) {
+  if (fmt == 1) {  // bf16x3 operands, fp16 output: the layer in front of a group
+    if (!pair && mt == 2 && bn == 128 && bk == 32 && cw == 32) return (ConvKernelFn)conv_tc_kernel<128, 32, 3, 32, false, 2, 1>;
+    if (pair && bn == 256 && bk == 64 && cw == 32) return (ConvKernelFn)conv_tc_kernel<256, 64, 3, 32, true, 1, 1>;
+    return nullptr;
+  }
+  if (fmt == 2) {  // fp16 operands and output
+    if (pair && bn == 256 && bk == 64 && cw == 32) return (ConvKernelFn)conv_tc_kernel<256, 64, 1, 32, true, 1, 2>;
+    if (!pair && mt == 2 && bn == 128 && bk == 32 && cw == 32) return (ConvKernelFn)conv_tc_kernel<128, 32, 1, 32, false, 2, 2>;
+    if (!pair && mt == 1 && bn == 128 && bk == 64 && cw == 64) return (ConvKernelFn)conv_tc_kernel<128, 64, 1, 64, false, 1, 2>;
+    if (!pair && mt == 1 && bn == 128 && bk == 64 && cw == 32) return (ConvKernelFn)conv_tc_kernel<128, 64, 1, 32, false, 1, 2>;
+    return nullptr;
+  }
+  if (fmt == 3) {  // fp16 operands, bf16 hi/lo output: the last layer of a group (a transposed conv)
+    if (pair && bn == 256 && bk == 64 && cw == 32) return (ConvKernelFn)conv_tc_kernel<256, 64, 1, 32, true, 1, 3>;
+    return nullptr;
+  }
+  return nullptr;
+}
+ConvKernelFn layer_kernel(const b200al_ctx* ctx, const Layer& L) {
+  if (L.fmt) return pick_kernel_fmt(L.bn, L.bk, L.cw, L.pair, L.mt, L.fmt);
+  return pick_kernel(L.bn, L.bk, layer_nsplit(ctx, L), L.cw, L.pair, L.mt);
+}
+int layer_smem(const b200al_ctx* ctx, const Layer& L) {
+  return conv_smem_bytes(L.bn, L.bk, layer_nsplit(ctx, L), layer_oplanes(ctx, L), L.stages, L.cw, L.nbuf * L.ngroups,
+                         L.pair, L.mt);
+}
+}  // namespace
+
 // ---------------------------------------------------------------------------
 // context
 // ---------------------------------------------------------------------------
@@ -567,11 +621,13 @@ void add_conv(b200al_ctx* ctx, int block, int cin, int cout, int stride, ActView
   Layer L;
   L.kind = KIND_CONV3; L.cin = cin; L.cout = cout; L.stride = stride; L.in = in; L.out = out;
   L.block = block; L.mask_off = mask_off;
+  L.index = (int)ctx->layers.size();
   ctx->layers.push_back(L);
 }
 void add_convT(b200al_ctx* ctx, int up, int cin, int cout, ActView in, ActView out) {
   Layer L;
   L.kind = KIND_CONVT; L.cin = cin; L.cout = cout; L.stride = 1; L.in = in; L.out = out; L.up = up;
+  L.index = (int)ctx->layers.size();
   ctx->layers.push_back(L);
 }
 
@@ -613,6 +669,64 @@ constexpr int kEncoderLayers = 9;  // layers[0..8] end at the bottleneck (E4B)
 
 }  // namespace
 
+namespace {
+// Weight map, kernel attributes and residency of a layer that runs on the generic kernel (either layer list).
+int finish_generic_layer(b200al_ctx* ctx, Layer& L) {
+  int rc;
+  if (L.fmt >= 2) {  // single fp16 plane: rows [taps][N]
+    if ((rc = make_tma_wgt(ctx, &L.tmB, reinterpret_cast<const __nv_bfloat16*>(L.wp16), L.p.taps * L.p.n_total, L.cin,
+                           L.bk, L.bn / 2)))
+      return rc;
+  } else {
+    // rows: conv [2 planes][9 taps][Cout]; convT [2 planes][1][4*Cout]
+    // (boxes of BN/2 rows: a weight tile is fetched as two halves, see conv_tc.cuh)
+    if ((rc = make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn / 2))) return rc;
+  }
+  ConvKernelFn fn = layer_kernel(ctx, L);
+  if (!fn)
+    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d CW=%d pair=%d mt=%d fmt=%d (layer %d)", L.bn,
+                   L.bk, L.cw, (int)L.pair, L.mt, L.fmt, L.index);
+  const int smem_l = layer_smem(ctx, L);
+  CUDA_TRY(ctx, cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+  int occ = 0;
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kConvThreads, smem_l));
+  const int tmem_limit = 512 / (2 * L.mt * L.bn);  // two accumulator stages per CTA
+  L.ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
+  if (L.ctas_per_sm > 2) L.ctas_per_sm = 2;
+  if (L.pair || L.mt == 2) L.ctas_per_sm = 1;
+  if (env_int("B200AL_VERBOSE", 0))
+    fprintf(stderr, "b200al plan: layer %d kind=%d %d->%d s%d fmt=%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d pair=%d mt=%d\n",
+            L.index, L.kind, L.cin, L.cout, L.stride, L.fmt, L.bn, L.bk, L.stages, L.cw, L.nbuf, L.ngroups, smem_l,
+            L.ctas_per_sm, (int)L.pair, L.mt);
+  return 0;
+}
+
+// B200AL_MIXED / B200AL_MIXED_DEEP: the scoring path's own copy of the layer list with an fp16 group in the deep part
+// of the network (where single fp16 operands cost <= 4e-3 of logit error per layer, profiles/r02_precision.json).
+int build_mix_layers(b200al_ctx* ctx, int entry, int first, int last) {
+  ctx->mix_layers = ctx->layers;  // same buffers, maps, affine tables; bf16x3 plans outside the group
+  ctx->mix_first = first;
+  ctx->mix_last = last;
+  for (int i = entry; i <= last; ++i) {
+    Layer& L = ctx->mix_layers[i];
+    if (L.fold) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "layer %d of the fp16 group runs on the folded kernel", i);
+    L.fmt = i == entry ? 1 : (i == last ? 3 : 2);
+    L.nsplit = i == entry ? 3 : 1;
+    int rc;
+    if ((rc = plan_layer(ctx, L))) return rc;
+    if (L.fold) return set_err(ctx, B200AL_ERR_UNSUPPORTED, "layer %d of the fp16 group was planned as folded", i);
+    if (L.fmt >= 2) {
+      const int taps = L.kind == KIND_CONV3 ? 9 : 4;
+      if ((rc = dev_alloc(ctx, &L.wp16, (size_t)taps * L.cout * L.cin))) return rc;
+    }
+    if ((rc = make_layer_maps(ctx, L, ctx->bufs[L.in.buf].ptr, ctx->bufs[L.out.buf].ptr, ctx->max_samples, &L.tmA, &L.tmO)))
+      return rc;
+    if ((rc = finish_generic_layer(ctx, L))) return rc;
+  }
+  return 0;
+}
+}  // namespace
+
 extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int in_channels, int H, int W,
                                  int max_samples, int precision) {
   if (!out) return set_err(nullptr, B200AL_ERR_ARG, "out is NULL");
@@ -624,7 +738,7 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
   if (H < 128 || W < 256 || H % 128 || W % 256)
     return set_err(nullptr, B200AL_ERR_UNSUPPORTED, "H must be a multiple of 128 and W of 256 (got %dx%d)", H, W);
   if (max_samples < 1) return set_err(nullptr, B200AL_ERR_ARG, "max_samples must be >= 1");
-  if (precision != B200AL_BF16X3 && precision != B200AL_BF16) return set_err(nullptr, B200AL_ERR_ARG, "bad precision");
+  if (precision < B200AL_BF16X3 || precision > B200AL_MIXED_DEEP) return set_err(nullptr, B200AL_ERR_ARG, "bad precision");
   int ndev = 0;
   if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev <= 0)
     return set_err(nullptr, B200AL_ERR_CUDA, "no CUDA device visible: libb200al has no CPU fallback");
@@ -635,7 +749,7 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
                    prop.minor);
   b200al_ctx* ctx = new b200al_ctx();
   ctx->device = device; ctx->K = num_out; ctx->H = H; ctx->W = W; ctx->max_samples = max_samples;
-  ctx->precision = precision; ctx->nsplit = precision == B200AL_BF16X3 ? 3 : 1;
+  ctx->precision = precision; ctx->nsplit = precision == B200AL_BF16 ? 1 : 3;
   ctx->sm_count = prop.multiProcessorCount;
   int rc = 0;
 #define TRY_RC(x) do { rc = (x); if (rc) { g_last_error = ctx->err; b200al_ctx_destroy(ctx); return rc; } } while (0)
@@ -678,23 +792,10 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
                 fold_smem_bytes(L.cin, ctx->nsplit, L.slots));
       continue;
     }
-    // rows: conv [2 planes][9 taps][Cout]; convT [2 planes][1][4*Cout]
-    // (boxes of BN/2 rows: a weight tile is fetched as two halves, see conv_tc.cuh)
-    TRY_RC(make_tma_wgt(ctx, &L.tmB, L.wp, 2 * L.p.taps * L.p.n_total, L.cin, L.bk, L.bn / 2));
-    ConvKernelFn fn = pick_kernel(L.bn, L.bk, ctx->nsplit, L.cw, L.pair, L.mt);
-    if (!fn) { rc = set_err(ctx, B200AL_ERR_UNSUPPORTED, "no kernel for BN=%d BK=%d CW=%d", L.bn, L.bk, L.cw); b200al_ctx_destroy(ctx); return rc; }
-    const int smem_l = conv_smem_bytes(L.bn, L.bk, ctx->nsplit, L.stages, L.cw, L.nbuf * L.ngroups, L.pair, L.mt);
-    TRY_CU(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
-    int occ = 0;
-    TRY_CU(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, fn, kConvThreads, smem_l));
-    const int tmem_limit = 512 / (2 * L.mt * L.bn);  // two accumulator stages per CTA
-    L.ctas_per_sm = occ < 1 ? 1 : (occ > tmem_limit ? tmem_limit : occ);
-    if (L.ctas_per_sm > 2) L.ctas_per_sm = 2;
-    if (L.pair || L.mt == 2) L.ctas_per_sm = 1;
-    if (env_int("B200AL_VERBOSE", 0))
-      fprintf(stderr, "b200al plan: kind=%d %d->%d s%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d pair=%d mt=%d\n", L.kind,
-              L.cin, L.cout, L.stride, L.bn, L.bk, L.stages, L.cw, L.nbuf, L.ngroups, smem_l, L.ctas_per_sm, (int)L.pair, L.mt);
+    TRY_RC(finish_generic_layer(ctx, L));
   }
+  if (precision == B200AL_MIXED) TRY_RC(build_mix_layers(ctx, 3, 4, 15));       // enc2.0 | enc2.1 .. up2
+  if (precision == B200AL_MIXED_DEEP) TRY_RC(build_mix_layers(ctx, 5, 6, 12));  // enc3.0 | enc3.1 .. up1
   TRY_RC(dev_alloc(ctx, &ctx->first_w, 32 * 9));
   TRY_RC(dev_alloc(ctx, &ctx->first_bias, 32));
   TRY_RC(dev_alloc(ctx, &ctx->first_scale, 32));
@@ -785,6 +886,15 @@ extern "C" int b200al_load_weights(b200al_ctx* ctx, const b200al_weights* w, voi
     L.p.scale = L.scale; L.p.bias = L.bias; L.p.shift = L.shift;
     ctx->launches += 2;
   }
+  for (size_t i = 0; i < ctx->mix_layers.size(); ++i) {  // the scoring path's copies share the affine tables
+    Layer& M = ctx->mix_layers[i];
+    const Layer& L = ctx->layers[i];
+    M.p.slope = L.p.slope; M.p.scale = L.scale; M.p.bias = L.bias; M.p.shift = L.shift;
+    if (M.fmt < 2) continue;
+    if (M.kind == KIND_CONV3) pack_conv3x3_f16_kernel<<<256, 256, 0, st>>>(w->blocks[M.block].d_conv_weight, M.wp16, M.cout, M.cin);
+    else pack_convT_f16_kernel<<<256, 256, 0, st>>>(w->d_up_weight[M.up], M.wp16, M.cin, M.cout);
+    ctx->launches++;
+  }
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->head_w, w->d_head_weight, (size_t)ctx->K * 32 * sizeof(float),
                                 cudaMemcpyDeviceToDevice, st));
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->head_b, w->d_head_bias, (size_t)ctx->K * sizeof(float), cudaMemcpyDeviceToDevice, st));
@@ -824,9 +934,12 @@ int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, const float
 
 // layers [0, n_layers) of ctx->layers on S samples; mask nullable [S][2944]
 // head_logits non-null: the last layer applies the fused seg_output head and writes logits there
-int run_layers(b200al_ctx* ctx, int n_layers, int S, const float* mask, cudaStream_t st, float* head_logits = nullptr) {
+// mixed: the scoring path's layer list (fp16 group in the deep layers) when the context was created with one
+int run_layers(b200al_ctx* ctx, int n_layers, int S, const float* mask, cudaStream_t st, float* head_logits = nullptr,
+               bool mixed = false) {
+  std::vector<Layer>& layers = (mixed && !ctx->mix_layers.empty()) ? ctx->mix_layers : ctx->layers;
   for (int i = 0; i < n_layers; ++i) {
-    Layer& L = ctx->layers[i];
+    Layer& L = layers[i];
     ConvTcParams p = L.p;
     p.mask = (mask && L.kind == KIND_CONV3) ? mask + L.mask_off : nullptr;
     int rc = launch_conv(ctx, L, L.tmA, L.tmO, p, S, st, i == n_layers - 1 ? head_logits : nullptr);
@@ -954,7 +1067,7 @@ extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int ima
   if (ctx->fuse_head) {
     // last decoder block + seg_output fused: logits [S][K][HW] fp32, then the HBM-bound softmax/score reduction
     float* lg = d_logits_out ? d_logits_out : ctx->logits_buf;
-    if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st, lg))) return rc;
+    if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st, lg, true))) return rc;
     const int HW = ctx->H * ctx->W;
     if ((HW / 4 + 255) / 256 < nblk) nblk = (HW / 4 + 255) / 256;
     if (mode == B200AL_DICE) {
@@ -969,7 +1082,7 @@ extern "C" int b200al_unet_scores(b200al_ctx* ctx, const void* d_images, int ima
     DISPATCH_K(ctx->K, CALL_UNC)
 #undef CALL_UNC
   } else {
-    if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st))) return rc;
+    if ((rc = run_layers(ctx, (int)ctx->layers.size(), S, mask, st, nullptr, true))) return rc;
     float* lg = mode == B200AL_DICE ? (d_logits_out ? d_logits_out : ctx->logits_buf) : d_logits_out;
 #define CALL_HEAD(KK) launch_head<KK>(ctx, n, T, mode == B200AL_DICE ? 0 : mode, smooth, lg, st)
     DISPATCH_K(ctx->K, CALL_HEAD)

@@ -5,6 +5,7 @@
 
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -260,6 +261,11 @@ __device__ __forceinline__ void umma_commit_mc(uint32_t bar, uint16_t cta_mask) 
 // kind::f16 instruction descriptor: fp32 accumulate, bf16 A/B, both K-major.
 __host__ __device__ constexpr uint32_t umma_idesc_bf16(uint32_t M, uint32_t N) {
   return (1u << 4) /*D=f32*/ | (1u << 7) /*A=bf16*/ | (1u << 10) /*B=bf16*/ | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+
+// the same with fp16 A/B (a_format = b_format = 0): the single-plane layers of the mixed-precision scoring path
+__host__ __device__ constexpr uint32_t umma_idesc_f16(uint32_t M, uint32_t N) {
+  return (1u << 4) /*D=f32*/ | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
 
 // Shared-memory matrix descriptor, K-major operand, rows of `row_bytes`

@@ -61,15 +61,21 @@ struct ConvTcParams {
 
 constexpr int kConvThreads = 320;  // TMA warp + MMA warp + 2 epilogue groups of 4 warps
 
+// FMT (mixed-precision scoring path): 0 = operands and output as NSPLIT says (bf16 hi/lo pair, or hi plane only);
+// 1 = bf16 hi/lo operands (NSPLIT == 3), output ONE fp16 plane (the layer in front of an fp16 group);
+// 2 = single fp16 operands (NSPLIT == 1, one MMA per k-step, kind::f16 with f16 formats), output one fp16 plane;
+// 3 = single fp16 operands, output a bf16 hi/lo pair again (last layer of an fp16 group).
+// A single plane always sits where the hi plane of the pair would (the lo half of the pixel stays unused).
 // smem: [stages x (A planes, B planes)] [nbuf x planes x 128 x CW staging for the TMA store] [barriers] [affine]
-template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR = false, int MT = 1>
+template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR = false, int MT = 1, int FMT = 0>
 struct ConvTcSmem {
   static constexpr int kPlanes = (NSPLIT == 3) ? 2 : 1;
+  static constexpr int kOutPlanes = FMT == 0 ? kPlanes : (FMT == 3 ? 2 : 1);
   static constexpr int kABytes = 128 * BK * 2;
   static constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * BK * 2;  // rows of B held by this CTA
   static constexpr int kStageBytes = kPlanes * (MT * kABytes + kBBytes);  // [A tile(s): hi, lo per tile][B: hi, lo]
   static constexpr int kOutWarpBytes = 32 * CW * 2;                  // one warp's 32 rows of one plane
-  static constexpr int kOutBufBytes = kPlanes * 4 * kOutWarpBytes;   // one staging buffer
+  static constexpr int kOutBufBytes = kOutPlanes * 4 * kOutWarpBytes;   // one staging buffer
   static constexpr int kTailBytes = 1024;  // barriers, tmem ptr
 };
 
@@ -107,12 +113,16 @@ __device__ __forceinline__ bool get_tile(const ConvTcParams& p, int i, int block
   return true;
 }
 
-template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR, int MT = 1>
+template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR, int MT = 1, int FMT = 0>
 __global__ void __launch_bounds__(kConvThreads)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const ConvTcParams p, const int stages, const int nbuf, const int ngroups) {
-  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW, PAIR, MT>;
+  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW, PAIR, MT, FMT>;
   static_assert(BLOCK_N % CW == 0 && (CW == 32 || CW == 64), "bad store chunk width");
+  static_assert(FMT == 0 || (FMT == 1 && NSPLIT == 3) || ((FMT == 2 || FMT == 3) && NSPLIT == 1), "bad operand format");
+  constexpr bool A16 = FMT >= 2;              // fp16 operands
+  constexpr bool O16 = FMT == 1 || FMT == 2;  // one fp16 output plane
+  constexpr int OPL = L::kOutPlanes;
   static_assert(MT == 1 || (MT == 2 && !PAIR && 4 * BLOCK_N <= 512), "super-tiles: two pixel tiles, one CTA");
   constexpr uint32_t kRowBytes = BK * 2;  // 128 -> SW128, 64 -> SW64
   // Stacked B (N <= 64, bf16x3): one tcgen05.mma costs max(math, shared-memory operand read) and the 128-row A
@@ -227,7 +237,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // The whole warp walks the loop (uniform control flow keeps the descriptor arithmetic on the
     // uniform datapath); one elected lane issues the MMAs and commits.
     if (!PAIR || rank == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(PAIR ? 256 : 128, BLOCK_N);
+      constexpr uint32_t idesc = A16 ? umma_idesc_f16(PAIR ? 256 : 128, BLOCK_N) : umma_idesc_bf16(PAIR ? 256 : 128, BLOCK_N);
       constexpr uint32_t kDescHi = umma_smem_desc_hi(kRowBytes);
       const uint32_t ring_lo = umma_smem_desc_lo(smem_u32(smem));
       int stage = 0;
@@ -371,10 +381,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             float y1f = fmaf(__uint_as_float(v[2 * j + 1]), sc2.y, sh2.y);
             y0f = fmaxf(y0f, y0f * p.slope);  // LeakyReLU for 0 <= slope <= 1 (checked on the host)
             y1f = fmaxf(y1f, y1f * p.slope);
+            if (O16) {
+              const __half2 f2 = __floats2half2_rn(y0f, y1f);
+              hi[j] = *reinterpret_cast<const uint32_t*>(&f2);
+              continue;
+            }
             const __nv_bfloat162 h2 = __floats2bfloat162_rn(y0f, y1f);
             const uint32_t hb = *reinterpret_cast<const uint32_t*>(&h2);
             hi[j] = hb;
-            if (NSPLIT == 3) {
+            if (OPL == 2) {
               const __nv_bfloat162 l2 =
                   __floats2bfloat162_rn(y0f - __uint_as_float(hb << 16), y1f - __uint_as_float(hb & 0xffff0000u));
               lo[j] = *reinterpret_cast<const uint32_t*>(&l2);
@@ -387,7 +402,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             const uint32_t off = (CW == 64) ? (uint32_t)(lane * 128 + ((chunk ^ (lane & 7)) << 4))
                                             : (uint32_t)(lane * 64 + ((chunk ^ ((lane >> 1) & 3)) << 4));
             *reinterpret_cast<uint4*>(sub_hi + off) = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
-            if (NSPLIT == 3)
+            if (OPL == 2)
               *reinterpret_cast<uint4*>(sub_lo + off) =
                   make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
           }
@@ -403,7 +418,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
         if (elect_one()) {
           tma_store_5d(&tmO, smem_u32(sub_hi), coff + p.out_hi_off + cbase, cx, cp, cy, tc.sample);
-          if (NSPLIT == 3) tma_store_5d(&tmO, smem_u32(sub_lo), coff + p.out_lo_off + cbase, cx, cp, cy, tc.sample);
+          if (OPL == 2) tma_store_5d(&tmO, smem_u32(sub_lo), coff + p.out_lo_off + cbase, cx, cp, cy, tc.sample);
           tma_store_commit();
         }
         if (++obuf == nbuf) obuf = 0;

@@ -54,6 +54,27 @@ __global__ void pack_convT_kernel(const float* __restrict__ w, __nv_bfloat16* __
   }
 }
 
+// Single-plane fp16 packings of the same two layouts (plane 0 only) for the fp16 layers of the mixed-precision
+// scoring path (conv_tc.cuh, FMT >= 2).
+__global__ void pack_conv3x3_f16_kernel(const float* __restrict__ w, __half* __restrict__ wp, int cout, int cin) {
+  const int total = cout * cin * 9;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int tap = i % 9;
+    const int ci = (i / 9) % cin;
+    const int co = i / (9 * cin);
+    wp[((size_t)tap * cout + co) * cin + ci] = __float2half_rn(w[i]);
+  }
+}
+__global__ void pack_convT_f16_kernel(const float* __restrict__ w, __half* __restrict__ wp, int cin, int cout) {
+  const int total = cin * cout * 4;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int quad = i % 4;
+    const int co = (i / 4) % cout;
+    const int ci = i / (4 * cout);
+    wp[((size_t)quad * cout + co) * cin + ci] = __float2half_rn(w[i]);
+  }
+}
+
 // BatchNorm (eval) folded to y = (acc + bias) * scale + shift (blocks.py:98;
 // Dropout2d sits between conv and BN, so the MC mask multiplies `scale`).
 __global__ void fold_bn_kernel(const float* gamma, const float* beta, const float* mean, const float* var, float eps,

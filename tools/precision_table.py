@@ -90,6 +90,8 @@ def forward(sd, x, fmts, storage):
     head (fused epilogue) run in fp32 in the product path and stay fp32 here."""
     blocks = plain_blocks(1)
     li = 0
+    if isinstance(storage, str):
+        storage = [storage] * 22
 
     def block(i, z):
         nonlocal li
@@ -99,7 +101,7 @@ def forward(sd, x, fmts, storage):
         y = y + sd[f"{prefix}.0.bias"][None, :, None, None]
         y = F.batch_norm(y, sd[f"{prefix}.2.running_mean"], sd[f"{prefix}.2.running_var"], sd[f"{prefix}.2.weight"],
                          sd[f"{prefix}.2.bias"], training=False, eps=BN_EPS)
-        return store(F.leaky_relu(y, LEAKY_SLOPE), storage)
+        return store(F.leaky_relu(y, LEAKY_SLOPE), storage[li - 1])
 
     skips = []
     z = x
@@ -111,7 +113,7 @@ def forward(sd, x, fmts, storage):
     for l in range(4):
         y = contract(lambda a, w: F.conv_transpose2d(a, w, None, stride=2), y, sd[f"decoder.upsamples.{l}.weight"], fmts[li])
         li += 1
-        y = store(y + sd[f"decoder.upsamples.{l}.bias"][None, :, None, None], storage)
+        y = store(y + sd[f"decoder.upsamples.{l}.bias"][None, :, None, None], storage[li - 1])
         y = torch.cat([skips[3 - l], y], dim=1)
         y = block(10 + 2 * l, y)
         y = block(11 + 2 * l, y)
@@ -121,6 +123,27 @@ def forward(sd, x, fmts, storage):
 
 LAYER_NAMES = [f"encoder.levels.{l}.{j}" for l in range(5) for j in range(2)] + \
     [n for l in range(4) for n in (f"decoder.upsamples.{l}", f"decoder.levels.{l}.0", f"decoder.levels.{l}.1")]
+
+
+# Per-layer precision mixes of the product path (layer indices as in LAYER_NAMES): the layers of `group` contract
+# single fp16 operands (1 MMA, one plane); `entry` (bf16x3 itself) already stores its output as single fp16 for them,
+# the last layer of the group stores a bf16 hi/lo pair again for the bf16x3 layers that follow.
+MIXES = {
+    "deep": {"entry": 6, "group": list(range(7, 14))},    # enc3.1 .. up1    (entry: enc3.0)
+    "wide": {"entry": 4, "group": list(range(5, 17))},    # enc2.1 .. up2    (entry: enc2.0)
+}
+
+
+def mix_formats(name):
+    m = MIXES[name]
+    fmts = ["fp32"] + ["bf16x3"] * 21
+    sto = ["bf16x3"] * 22
+    for i in m["group"]:
+        fmts[i] = "fp16"
+        sto[i] = "fp16"
+    sto[m["entry"]] = "fp16"
+    sto[m["group"][-1]] = "bf16x3"
+    return fmts, sto
 
 
 def main():
@@ -158,6 +181,14 @@ def main():
             out["whole_net"][fmt] = r
             print(f"whole net {fmt:7s} logit {r['max_abs_logit_err']:.3e} score {r['max_rel_score_err']:.3e} "
                   f"{'ok' if r['meets_tolerance'] else 'FAILS'}  ({time.time() - t0:.0f}s)", flush=True)
+        out["mixes"] = {}
+        for name in MIXES:
+            fm, sto = mix_formats(name)
+            r = measure(fm, sto)
+            r["fp16_layers"] = [LAYER_NAMES[i] for i in MIXES[name]["group"]]
+            r["entry_layer"] = LAYER_NAMES[MIXES[name]["entry"]]
+            out["mixes"][name] = r
+            print(f"mix {name:5s} logit {r['max_abs_logit_err']:.3e} score {r['max_rel_score_err']:.3e}", flush=True)
         if not args.no_layers:
             for fmt in ("fp16", "fp16x2", "bf16"):
                 rows = {}
