@@ -143,9 +143,18 @@ int b200al_badge_embed(b200al_ctx* ctx, const void* d_images, int image_dtype, c
 int b200al_uncertainty_from_logits(b200al_ctx* ctx, const float* d_logits, int n, int T, int K, int HW, int mode,
                                    float smooth, float* d_scores_out, void* stream);
 
+/* Scratch of b200al_topk and b200al_kcenter_fused lives in a workspace owned by the context.  It is allocated ONLY by
+ * b200al_workspace_reserve (grows to at least `bytes`; synchronises the device when it reallocates) - the hot calls
+ * themselves never allocate and return B200AL_ERR_STATE when the workspace is too small.  The *_bytes functions give
+ * the size a call needs (no reference counterpart: the reference lets torch / numpy allocate as they go). */
+size_t b200al_workspace_bytes_topk(int n);
+size_t b200al_workspace_bytes_kcenter_fused(int n, int D1, int D2, int metric);
+int b200al_workspace_reserve(b200al_ctx* ctx, size_t bytes);
+
 /* Rank & cut (entropy_selector.py:76-82): k best of n scores, descending,
  * ties -> lower position first.  Writes k' = min(k,n) entries; positions are
- * base_pos + index.  d_out_scores [k'], d_out_pos [k'] int64. */
+ * base_pos + index.  d_out_scores [k'], d_out_pos [k'] int64.
+ * Needs b200al_workspace_bytes_topk(n) bytes of reserved workspace. */
 int b200al_topk(b200al_ctx* ctx, const float* d_scores, int n, int k, int64_t base_pos, float* d_out_scores,
                 int64_t* d_out_pos, void* stream);
 
@@ -169,7 +178,8 @@ int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int me
  * fl32(1 - w) computed by the caller in double like the reference's python expression) over rows 0..n-1 of the two
  * feature matrices d_emb [n,D1] (D1 <= 1024) and d_loaded [n,D2] (any width); rows 0..n_init-1 are the labeled set.
  * The two global pair-distance sums are computed on the device (one O(n^2) pass each, no n x n matrix).
- * d_picks [budget] int64 in selection order (-1 when exhausted), d_pick_vals nullable.  Synchronises the stream. */
+ * d_picks [budget] int64 in selection order (-1 when exhausted), d_pick_vals nullable.  Asynchronous on `stream`;
+ * needs b200al_workspace_bytes_kcenter_fused(n, D1, D2, metric) bytes of reserved workspace. */
 int b200al_kcenter_fused(b200al_ctx* ctx, const float* d_emb, int D1, const float* d_loaded, int D2, int n, int n_init,
                          int metric, int criteria, float loaded_weight, float emb_weight, int budget,
                          int64_t* d_picks, float* d_pick_vals, void* stream);

@@ -68,6 +68,9 @@ PROTOTYPES = {
     "b200al_unet_embed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "b200al_uncertainty_from_logits": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                                  C.c_float, C.c_void_p, C.c_void_p]),
+    "b200al_workspace_bytes_topk": (C.c_size_t, [C.c_int]),
+    "b200al_workspace_bytes_kcenter_fused": (C.c_size_t, [C.c_int, C.c_int, C.c_int, C.c_int]),
+    "b200al_workspace_reserve": (C.c_int, [C.c_void_p, C.c_size_t]),
     "b200al_topk": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200al_topk_static": (C.c_int, [C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200al_kcenter_init": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int,

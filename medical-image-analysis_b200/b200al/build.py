@@ -28,7 +28,8 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and up_to_date():
         return OUT
     nvcc = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
-    cmd = [nvcc] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(CSRC, "b200al.cu")]
+    tuning = ["-DB200AL_TUNING"] if os.environ.get("B200AL_TUNING_BUILD") else []  # planner / debug env switches
+    cmd = [nvcc] + NVCC_FLAGS + tuning + (["-Xptxas", "-v"] if verbose else []) + ["-o", OUT, os.path.join(CSRC, "b200al.cu")]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + res.stdout + res.stderr)

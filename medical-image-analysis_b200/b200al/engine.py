@@ -289,6 +289,14 @@ class Engine:
                                                                 self._stream()))
         return out
 
+    def _reserve(self, nbytes: int) -> None:
+        """Grow the context's scratch workspace (the only allocation of the rank / fused k-center paths; the C calls
+        themselves never allocate)."""
+        if nbytes > getattr(self, "_ws_bytes", 0):
+            with torch.cuda.device(self.device):
+                self._check(self.lib.b200al_workspace_reserve(self.ctx, int(nbytes)))
+            self._ws_bytes = int(nbytes)
+
     # ------------------------------------------------------------ rank & cut
     def topk(self, scores: torch.Tensor, k: int, base_pos: int = 0):
         """k best (descending score, lower position on ties): (scores[k'], pos[k'] int64)."""
@@ -298,6 +306,7 @@ class Engine:
         vals = torch.empty(k, dtype=torch.float32, device=self.device)
         pos = torch.empty(k, dtype=torch.int64, device=self.device)
         if k:
+            self._reserve(self.lib.b200al_workspace_bytes_topk(n))
             with torch.cuda.device(self.device):
                 self._check(self.lib.b200al_topk(self.ctx, self._ptr(scores), n, k, int(base_pos), self._ptr(vals),
                                                  self._ptr(pos), self._stream()))
@@ -357,6 +366,8 @@ class Engine:
         picks = torch.empty(budget, dtype=torch.int64, device=self.device)
         vals = torch.empty(budget, dtype=torch.float32, device=self.device)
         if budget > 0:
+            self._reserve(self.lib.b200al_workspace_bytes_kcenter_fused(n, feats.shape[1], loaded.shape[1],
+                                                                        _lib.METRICS[metric]))
             with torch.cuda.device(self.device):
                 self._check(self.lib.b200al_kcenter_fused(
                     self.ctx, self._ptr(feats), feats.shape[1], self._ptr(loaded), loaded.shape[1], n, int(n_init),

@@ -116,9 +116,10 @@ struct b200al_ctx {
   float *kc_part_val = nullptr, *kc_centre = nullptr;
   int* kc_part_idx = nullptr;
   int kc_blocks = 0;
-  unsigned long long *tk_keys = nullptr, *tk_cand = nullptr;
-  size_t tk_cap = 0;
   TopkState* tk_state = nullptr;
+  // scratch of b200al_topk / b200al_kcenter_fused: sized by b200al_workspace_reserve, never inside a hot call
+  char* ws = nullptr;
+  size_t ws_bytes = 0;
   // bookkeeping
   long long launches = 0;
   bool timing = false;
@@ -337,9 +338,17 @@ int fold_smem_bytes(int cin, int nsplit, int slots) {
   return (cin == 32 ? 1 : planes) * 3 * kFoldN * row + slots * 6 * 32 * row + 8 * planes * 2048 + 3072;
 }
 
+// Planner / debug switches (B200AL_VERBOSE, B200AL_MT2, B200AL_FOLD_DBG, ...) exist in TUNING builds only
+// (`B200AL_TUNING_BUILD=1 python -c "import __graft_entry__ as g; g.build()"` adds -DB200AL_TUNING; tools/ab.sh and
+// the experiments recorded in DESIGN.md used them).  The product library reads no environment variable.
 int env_int(const char* name, int dflt) {
+#ifdef B200AL_TUNING
   const char* v = getenv(name);
   return v ? atoi(v) : dflt;
+#else
+  (void)name;
+  return dflt;
+#endif
 }
 
 void choose_tile(int W, int* tw, int* th) {
@@ -830,8 +839,7 @@ extern "C" void b200al_ctx_destroy(b200al_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   for (void* p : ctx->allocs) cudaFree(p);
-  if (ctx->tk_keys) cudaFree(ctx->tk_keys);
-  if (ctx->tk_cand) cudaFree(ctx->tk_cand);
+  if (ctx->ws) cudaFree(ctx->ws);
   for (auto& e : ctx->ev)
     if (e) cudaEventDestroy(e);
   delete ctx;
@@ -1202,6 +1210,33 @@ extern "C" int b200al_uncertainty_from_logits(b200al_ctx* ctx, const float* d_lo
 }
 
 // ---------------------------------------------------------------------------
+// workspace (scratch of b200al_topk / b200al_kcenter_fused)
+// ---------------------------------------------------------------------------
+extern "C" size_t b200al_workspace_bytes_topk(int n) {
+  return n > 0 ? (size_t)n * 2 * sizeof(unsigned long long) : 0;
+}
+extern "C" size_t b200al_workspace_bytes_kcenter_fused(int n, int D1, int D2, int metric) {
+  if (n < 1 || D1 < 1 || D2 < 1) return 0;
+  const size_t nwarps = (size_t)148 * 8 * 8 * 2;  // upper bound of the partial-sum slots on any sm_100 part
+  const size_t norm = metric == B200AL_COSINE ? (size_t)n * ((size_t)D1 + (size_t)D2) * 4 : 0;
+  return (size_t)n * 8 + nwarps * 8 + 16 + (((size_t)n + 15) & ~(size_t)15) + norm + 256;
+}
+// Grows the context's workspace to at least `bytes` (synchronises the device when it has to reallocate; a no-op
+// otherwise).  The one place where this scratch is allocated: call it at set-up, not between hot calls.
+extern "C" int b200al_workspace_reserve(b200al_ctx* ctx, size_t bytes) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (bytes <= ctx->ws_bytes) return B200AL_OK;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  CUDA_TRY(ctx, cudaDeviceSynchronize());
+  if (ctx->ws) cudaFree(ctx->ws);
+  ctx->ws = nullptr;
+  ctx->ws_bytes = 0;
+  CUDA_TRY(ctx, cudaMalloc(&ctx->ws, bytes));
+  ctx->ws_bytes = bytes;
+  return B200AL_OK;
+}
+
+// ---------------------------------------------------------------------------
 // rank & cut
 // ---------------------------------------------------------------------------
 extern "C" int b200al_topk(b200al_ctx* ctx, const float* d_scores, int n, int k, int64_t base_pos,
@@ -1213,24 +1248,20 @@ extern "C" int b200al_topk(b200al_ctx* ctx, const float* d_scores, int n, int k,
   if (!d_scores || !d_out_scores || !d_out_pos) return set_err(ctx, B200AL_ERR_ARG, "NULL pointer");
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
-  if ((size_t)n > ctx->tk_cap) {
-    CUDA_TRY(ctx, cudaStreamSynchronize(st));
-    if (ctx->tk_keys) cudaFree(ctx->tk_keys);
-    if (ctx->tk_cand) cudaFree(ctx->tk_cand);
-    ctx->tk_keys = ctx->tk_cand = nullptr;
-    ctx->tk_cap = 0;
-    CUDA_TRY(ctx, cudaMalloc(&ctx->tk_keys, (size_t)n * sizeof(unsigned long long)));
-    CUDA_TRY(ctx, cudaMalloc(&ctx->tk_cand, (size_t)n * sizeof(unsigned long long)));
-    ctx->tk_cap = (size_t)n;
-  }
+  const size_t need = b200al_workspace_bytes_topk(n);
+  if (need > ctx->ws_bytes)
+    return set_err(ctx, B200AL_ERR_STATE, "b200al_topk: workspace of %zu bytes needed, %zu reserved - call "
+                   "b200al_workspace_reserve(ctx, b200al_workspace_bytes_topk(n)) first", need, ctx->ws_bytes);
+  unsigned long long* keys = reinterpret_cast<unsigned long long*>(ctx->ws);
+  unsigned long long* cand = keys + n;
   const int blocks = (n + 255) / 256 < ctx->sm_count * 8 ? (n + 255) / 256 : ctx->sm_count * 8;
-  topk_keys_kernel<<<blocks, 256, 0, st>>>(d_scores, n, ctx->tk_keys, ctx->tk_state, (unsigned)k);
+  topk_keys_kernel<<<blocks, 256, 0, st>>>(d_scores, n, keys, ctx->tk_state, (unsigned)k);
   for (int pass = 0; pass < 8; ++pass) {
-    topk_hist_kernel<<<blocks, 256, 0, st>>>(ctx->tk_keys, n, ctx->tk_state, pass);
+    topk_hist_kernel<<<blocks, 256, 0, st>>>(keys, n, ctx->tk_state, pass);
     topk_scan_kernel<<<1, 32, 0, st>>>(ctx->tk_state, pass);
   }
-  topk_compact_kernel<<<blocks, 256, 0, st>>>(ctx->tk_keys, n, ctx->tk_state, ctx->tk_cand, (unsigned)k);
-  topk_rank_kernel<<<(k + 255) / 256, 256, 0, st>>>(ctx->tk_cand, (unsigned)k, (long long)base_pos, d_out_scores,
+  topk_compact_kernel<<<blocks, 256, 0, st>>>(keys, n, ctx->tk_state, cand, (unsigned)k);
+  topk_rank_kernel<<<(k + 255) / 256, 256, 0, st>>>(cand, (unsigned)k, (long long)base_pos, d_out_scores,
                                                    (long long*)d_out_pos);
   ctx->launches += 19;
   CUDA_TRY(ctx, cudaGetLastError());
@@ -1394,8 +1425,13 @@ extern "C" int b200al_kcenter_fused(b200al_ctx* ctx, const float* d_emb, int D1,
   // scratch: state [n] doubles | partial [nwarps] doubles | sums [2] floats | taken [n] | normalised copies (cosine)
   const size_t norm_elems = metric == B200AL_COSINE ? (size_t)n * (D1 + D2) : 0;
   const size_t bytes = (size_t)n * 8 + (size_t)nwarps * 8 + 16 + (((size_t)n + 15) & ~(size_t)15) + norm_elems * 4;
-  char* scratch = nullptr;
-  CUDA_TRY(ctx, cudaMalloc(&scratch, bytes));
+  if (bytes > b200al_workspace_bytes_kcenter_fused(n, D1, D2, metric))
+    return set_err(ctx, B200AL_ERR_CUDA, "kcenter_fused: workspace size formula out of date");
+  if (bytes > ctx->ws_bytes)
+    return set_err(ctx, B200AL_ERR_STATE, "b200al_kcenter_fused: workspace of %zu bytes needed, %zu reserved - call "
+                   "b200al_workspace_reserve(ctx, b200al_workspace_bytes_kcenter_fused(n, D1, D2, metric)) first",
+                   bytes, ctx->ws_bytes);
+  char* scratch = ctx->ws;
   void* state = scratch;
   double* partial = (double*)(scratch + (size_t)n * 8);
   float* sums = (float*)(partial + nwarps);
@@ -1433,10 +1469,7 @@ extern "C" int b200al_kcenter_fused(b200al_ctx* ctx, const float* d_emb, int D1,
                                           (long long*)d_picks, d_pick_vals, step);
     ctx->launches += 2;
   }
-  cudaError_t e = cudaGetLastError();
-  if (e == cudaSuccess) e = cudaStreamSynchronize(st);
-  cudaFree(scratch);
-  if (e != cudaSuccess) return set_err(ctx, B200AL_ERR_CUDA, "kcenter_fused: %s", cudaGetErrorString(e));
+  CUDA_TRY(ctx, cudaGetLastError());
   return B200AL_OK;
 }
 

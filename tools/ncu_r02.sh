@@ -9,6 +9,7 @@ run() {  # name, which, kernel regex, count
   timeout 900 ncu --set full --clock-control none --import-source on -k "regex:$3" -c "$4" -f -o "gpurun_out/r02_ncu_$1" \
       python tools/ncu_targets.py "$2" > "gpurun_out/r02_ncu_$1.log" 2>&1
   python tools/ncu_summary.py "gpurun_out/r02_ncu_$1.ncu-rep" > "gpurun_out/r02_ncu_full_$1.csv" 2>> "gpurun_out/r02_ncu_$1.log"
+  rm -f "gpurun_out/r02_ncu_$1.ncu-rep"   # gpurun copies at most 64 MiB back: keep the condensed CSV only
   echo "$1: $(wc -l < gpurun_out/r02_ncu_full_$1.csv) rows"
 }
 run uncertainty_128 unc 'uncertainty_logits_kernel|dice_logits_kernel' 4
