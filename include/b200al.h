@@ -173,6 +173,23 @@ int b200al_kcenter_init(b200al_ctx* ctx, const float* d_emb, int n, int D, const
  * d_state / d_taken are updated in place. */
 int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, int criteria, int n_centres,
                        void* d_state, uint8_t* d_taken, int budget, int64_t* d_picks, float* d_pick_vals, void* stream);
+/* The same greedy loop with the rows SHARDED over `world` GPUs (one process per GPU; no reference counterpart - the
+ * reference is single-process): this rank owns rows [row_bases[rank], row_bases[rank+1]) = d_emb_local [n_local, D] with
+ * its own d_state / d_taken, and ONE kernel per rank runs all `budget` steps: per step it updates its rows, publishes
+ * its best (value, global row) as 16 bytes into every peer's mailbox over NVLink, waits for the peers' entries, and
+ * reads the winning row straight from its owner's shard.  No other data crosses the links, no collective is called.
+ * d_mail_local: this rank's mailbox (b200al_kcenter_mailbox_bytes(world) bytes, zeroed once when it is allocated);
+ * d_mail_peers[r] / d_emb_peers[r]: rank r's mailbox / shard rows as mapped into THIS process (peer-accessible memory,
+ * e.g. torch.distributed._symmetric_memory buffer_ptrs or cudaIpcOpenMemHandle; entry `rank` = the local pointers).
+ * epoch: call counter starting at 1, the same on every rank, incremented per call on the same mailboxes.
+ * timeout_ms > 0: a rank that waits longer for a peer traps instead of hanging the GPU.  Every rank gets the same
+ * d_picks (GLOBAL row indices, selection order).  world == 1 needs no peer pointers (what b200al_kcenter_run calls). */
+size_t b200al_kcenter_mailbox_bytes(int world);
+int b200al_kcenter_run_sharded(b200al_ctx* ctx, const float* d_emb_local, int n_local, int64_t row_base, int D,
+                               int metric, int criteria, int n_centres, void* d_state, uint8_t* d_taken, int budget,
+                               int64_t* d_picks, float* d_pick_vals, int world, int rank, int epoch,
+                               void* d_mail_local, void* const* d_mail_peers, const float* const* d_emb_peers,
+                               const int64_t* row_bases, int timeout_ms, void* stream);
 /* CoresetSelector with externally loaded features, coreset_fusion="add" (coreset_selector.py:110-157, 221-229):
  * k-center greedy on  loaded_weight * D_loaded / sum(D_loaded) + emb_weight * D_emb / sum(D_emb)  (emb_weight =
  * fl32(1 - w) computed by the caller in double like the reference's python expression) over rows 0..n-1 of the two

@@ -77,6 +77,11 @@ PROTOTYPES = {
                                       C.c_void_p, C.c_int, C.c_void_p]),
     "b200al_kcenter_run": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                                      C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "b200al_kcenter_mailbox_bytes": (C.c_size_t, [C.c_int]),
+    "b200al_kcenter_run_sharded": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_int, C.c_int,
+                                             C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_int, C.c_int,
+                                             C.c_int, C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                             C.POINTER(C.c_int64), C.c_int, C.c_void_p]),
     "b200al_normalize_rows": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]),
     "b200al_kernel_launches": (C.c_int, [C.c_void_p, C.POINTER(C.c_int64)]),
     "b200al_conv_time_ms": (C.c_int, [C.c_void_p, C.POINTER(C.c_float), C.POINTER(C.c_int64), C.POINTER(C.c_double)]),

@@ -115,3 +115,66 @@ def broadcast_draws(first: int, uniforms, device=None, src: int = 0, group=None)
     flat = torch.from_numpy(np.concatenate([[float(first)], np.asarray(uniforms, np.float64).reshape(-1)]))
     flat = broadcast_cpu(flat, src, group)
     return int(flat[0].item()), flat[1:].numpy().reshape(np.asarray(uniforms).shape)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Peer-accessible buffers for the sharded k-center kernel (b200al_kcenter_run_sharded): one symmetric byte buffer per
+# rank, [mailbox | embedding shard rows], mapped into every process of the group by torch's symmetric memory
+# (NVLink P2P / fabric handles).  torch only allocates and exchanges the handles; the kernel does the exchange itself.
+# ---------------------------------------------------------------------------------------------------------------
+_PEER_BUFFERS: dict = {}
+
+
+class PeerBuffers:
+    MAIL_ALIGN = 256
+    MAX_EPOCH = 30000
+
+    def __init__(self, device, rows_cap: int, width: int, mail_bytes: int, group=None):
+        import torch.distributed._symmetric_memory as symm
+        rank, ws = world()
+        self.device, self.rows_cap, self.width = torch.device(device), int(rows_cap), int(width)
+        self.mail_bytes = (int(mail_bytes) + self.MAIL_ALIGN - 1) // self.MAIL_ALIGN * self.MAIL_ALIGN
+        nbytes = self.mail_bytes + self.rows_cap * self.width * 4
+        self.buf = symm.empty(nbytes, dtype=torch.uint8, device=self.device)
+        self.buf.zero_()                      # mailbox tags start at 0 ("never written")
+        torch.cuda.synchronize(self.device)
+        self.handle = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.ptrs = [int(x) for x in self.handle.buffer_ptrs]
+        if len(self.ptrs) != ws or self.ptrs[rank] != self.buf.data_ptr():
+            raise RuntimeError("symmetric memory rendezvous returned unexpected peer pointers")
+        self.epoch = 0
+        dist.barrier(group=group)             # every rank's zeroing has landed before anybody publishes
+
+    def rows(self, n: int) -> torch.Tensor:
+        """float32 [n, width] view of this rank's shard area."""
+        if n > self.rows_cap:
+            raise ValueError("shard larger than the peer buffer")
+        return self.buf[self.mail_bytes:self.mail_bytes + n * self.width * 4].view(torch.float32).view(n, self.width)
+
+    def next_epoch(self, group=None) -> int:
+        self.epoch += 1
+        if self.epoch > self.MAX_EPOCH:       # tags would wrap: start over with clean mailboxes
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=group)
+            self.buf[:self.mail_bytes].zero_()
+            torch.cuda.synchronize(self.device)
+            dist.barrier(group=group)
+            self.epoch = 1
+        return self.epoch
+
+    def mail_ptrs(self):
+        return list(self.ptrs)
+
+    def row_ptrs(self):
+        return [p + self.mail_bytes for p in self.ptrs]
+
+
+def peer_buffers(device, rows_cap: int, width: int, mail_bytes: int, group=None) -> PeerBuffers:
+    """Cached per (device, capacity, width): the rendezvous is a collective and the mapping stays valid."""
+    dev = torch.device(device)
+    key = (dev.index, int(width))
+    pb = _PEER_BUFFERS.get(key)
+    if pb is None or pb.rows_cap < rows_cap:
+        # capacities must agree across ranks: they are derived from the pool size and the world size only
+        pb = _PEER_BUFFERS[key] = PeerBuffers(dev, rows_cap, width, mail_bytes, group)
+    return pb

@@ -348,6 +348,44 @@ class Engine:
                                                     self._ptr(taken), budget, self._ptr(picks), self._ptr(vals), st))
         return (picks, vals) if return_vals else picks
 
+    def normalize_rows(self, feats: torch.Tensor) -> torch.Tensor:
+        """sklearn normalize() as cosine distances apply it (fp32, zero rows untouched)."""
+        feats = feats.to(device=self.device, dtype=torch.float32).contiguous()
+        out = torch.empty_like(feats)
+        if feats.shape[0]:
+            with torch.cuda.device(self.device):
+                self._check(self.lib.b200al_normalize_rows(self.ctx, self._ptr(feats), self._ptr(out), feats.shape[0],
+                                                           feats.shape[1], self._stream()))
+        return out
+
+    def kcenter_sharded(self, shard: torch.Tensor, centres: torch.Tensor, row_base: int, row_bases: list, budget: int,
+                        metric: str, criteria: str, rank: int, world: int, epoch: int, mail_ptrs: list, row_ptrs: list,
+                        timeout_ms: int = 20000) -> torch.Tensor:
+        """k-center greedy with the rows sharded over `world` ranks (b200al_kcenter_run_sharded): `shard` = this
+        rank's rows [n_local, D] (already normalised for cosine) living in peer-accessible memory, `centres` = the
+        initial centres (labeled rows, the same on every rank).  Returns GLOBAL row indices, the same on every rank."""
+        n_local, D = shard.shape
+        centres = centres.to(device=self.device, dtype=torch.float32).contiguous()
+        if criteria not in _lib.CRITERIA:
+            raise RuntimeError(f"coreset_criteria {criteria} is undefined")
+        m, c = _lib.METRICS[metric], _lib.CRITERIA[criteria]
+        state = torch.empty(max(n_local, 1), dtype=torch.float64 if criteria == "mean" else torch.float32,
+                            device=self.device)
+        taken = torch.zeros(max(n_local, 1), dtype=torch.uint8, device=self.device)
+        picks = torch.empty(budget, dtype=torch.int64, device=self.device)
+        st = self._stream()
+        PtrArr, I64Arr = C.c_void_p * world, C.c_int64 * (world + 1)
+        with torch.cuda.device(self.device):
+            if n_local:
+                self._check(self.lib.b200al_kcenter_init(self.ctx, self._ptr(shard), n_local, D, self._ptr(centres),
+                                                         centres.shape[0], m, c, self._ptr(state), 0, st))
+            self._check(self.lib.b200al_kcenter_run_sharded(
+                self.ctx, self._ptr(shard) if n_local else None, n_local, int(row_base), D, m, c, centres.shape[0],
+                self._ptr(state), self._ptr(taken), int(budget), self._ptr(picks), None, world, rank, int(epoch),
+                C.c_void_p(mail_ptrs[rank]), PtrArr(*mail_ptrs), PtrArr(*row_ptrs), I64Arr(*row_bases),
+                int(timeout_ms), st))
+        return picks
+
     def kcenter_fused(self, feats: torch.Tensor, loaded: torch.Tensor, loaded_weight: float, n_init: int, budget: int,
                       metric: str = "l2", criteria: str = "min", return_vals: bool = False):
         """k-center greedy on `w * D_loaded / sum(D_loaded) + (1 - w) * D_feats / sum(D_feats)` - CoresetSelector

@@ -408,8 +408,10 @@ class B200CoresetSelector(_B200Base):
 
     def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8,
                  metric: str = "cosine", coreset_criteria: str = "min", coreset_fusion: str = "add",
-                 feature_path=None, loaded_feature_weight: float = 0.0, feature_dict=None, **kw):
+                 feature_path=None, loaded_feature_weight: float = 0.0, feature_dict=None, shard_kcenter: bool = True,
+                 **kw):
         super().__init__(batch_size, num_workers, pin_memory, smooth, **kw)
+        self.shard_kcenter = bool(shard_kcenter)  # multi-GPU: sharded greedy loop (False: gather rows, run replicated)
         if metric not in ("l2", "cosine"):
             raise NotImplementedError(f"metric {metric!r}: only 'l2' and 'cosine' are supported")
         if coreset_criteria not in ("min", "mean"):
@@ -425,6 +427,29 @@ class B200CoresetSelector(_B200Base):
         self.coreset_fusion = coreset_fusion
         self.feature_path, self.feature_dict = feature_path, feature_dict
         self.loaded_feature_weight = float(loaded_feature_weight)
+
+    def _kcenter_sharded(self, eng: Engine, emb_l, emb_local, labeled_size, pool_size, select_num, rank, ws) -> list:
+        """Multi-GPU k-center without gathering the embeddings: every rank keeps the running state of its own pool
+        rows, and one kernel per rank runs all greedy steps, exchanging per step only its best (value, row) candidate
+        and reading the chosen centre from its owner's shard over NVLink (csrc/kcenter.cuh, kcenter_persist_kernel).
+        Global rows: 0..L-1 labeled (coreset_selector.py:85-88), L + p = pool position p."""
+        self._stages.start("kcenter")
+        _require_finite(emb_l, "embeddings")
+        _require_finite(emb_local, "embeddings")
+        if self.metric == "cosine":
+            emb_l, emb_local = eng.normalize_rows(emb_l), eng.normalize_rows(emb_local)
+        bases = [labeled_size + D.shard_range(pool_size, r, ws)[0] for r in range(ws)] + [labeled_size + pool_size]
+        cap = max(bases[r + 1] - bases[r] for r in range(ws))
+        pb = D.peer_buffers(eng.device, cap, emb_local.shape[1], eng.lib.b200al_kcenter_mailbox_bytes(ws))
+        shard = pb.rows(emb_local.shape[0])
+        shard.copy_(emb_local)
+        epoch = pb.next_epoch()
+        torch.cuda.synchronize(eng.device)
+        torch.distributed.barrier()   # every shard is in place before any rank's kernel reads a peer's rows
+        budget = min(int(select_num), pool_size)
+        picks = eng.kcenter_sharded(shard, emb_l, bases[rank], bases, budget, self.metric, self.coreset_criteria,
+                                    rank, ws, epoch, pb.mail_ptrs(), pb.row_ptrs())
+        return picks.tolist()
 
     def select_next_batch(self, active_dataset, select_num: int, model, device):
         import numpy as np
@@ -460,6 +485,9 @@ class B200CoresetSelector(_B200Base):
         self._stages.start("embed")
         emb_l = _embed_positions(eng, lsrc, list(range(labeled_size)))
         emb_local = _embed_positions(eng, psrc, list(range(lo, hi)))
+        if ws > 1 and not self.has_loaded and self.shard_kcenter:
+            picks = self._kcenter_sharded(eng, emb_l, emb_local, labeled_size, pool_size, select_num, rank, ws)
+            return [all_list[i] for i in _check_picks(picks, "k-center")]
         self._stages.start("gather")
         emb_p = D.gather_rows(emb_local)
         feats = torch.cat([emb_l, emb_p], 0)

@@ -116,6 +116,8 @@ struct b200al_ctx {
   float *kc_part_val = nullptr, *kc_centre = nullptr;
   int* kc_part_idx = nullptr;
   int kc_blocks = 0;
+  float* kc_pp_val = nullptr;      // [2][kc_blocks] partials of the persistent k-center kernel
+  long long* kc_pp_idx = nullptr;  // [2][kc_blocks]
   TopkState* tk_state = nullptr;
   // scratch of b200al_topk / b200al_kcenter_fused: sized by b200al_workspace_reserve, never inside a hot call
   char* ws = nullptr;
@@ -822,6 +824,8 @@ extern "C" int b200al_ctx_create(b200al_ctx** out, int device, int num_out, int 
   TRY_RC(dev_alloc(ctx, &ctx->kc_part_val, (size_t)ctx->kc_blocks));
   TRY_RC(dev_alloc(ctx, &ctx->kc_part_idx, (size_t)ctx->kc_blocks));
   TRY_RC(dev_alloc(ctx, &ctx->kc_centre, 2048));
+  TRY_RC(dev_alloc(ctx, &ctx->kc_pp_val, (size_t)2 * ctx->kc_blocks));
+  TRY_RC(dev_alloc(ctx, &ctx->kc_pp_idx, (size_t)2 * ctx->kc_blocks));
   TRY_RC(dev_alloc(ctx, &ctx->tk_state, 1));
   fill_kernel<<<2, 256>>>(ctx->ones, 1.0f, 512);
   fill_kernel<<<2, 256>>>(ctx->zeros, 0.0f, 512);
@@ -1568,6 +1572,88 @@ extern "C" int b200al_kmeans_pp(b200al_ctx* ctx, const float* d_X, int n, int D,
   return B200AL_OK;
 }
 
+namespace {
+template <int NV>
+int launch_kc_persist(b200al_ctx* ctx, KcPersistParams p, cudaStream_t st) {
+  int occ = 0;
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kcenter_persist_kernel<NV>, 256, 0));
+  if (occ < 1) return set_err(ctx, B200AL_ERR_CUDA, "persistent k-center kernel does not fit an SM");
+  int blocks = (p.n_local + 63) / 64;  // >= 8 rows per warp
+  const int resident = ctx->sm_count * (occ > 4 ? 4 : occ);  // a cooperative grid must be co-resident
+  if (blocks > resident) blocks = resident;
+  if (blocks > ctx->kc_blocks) blocks = ctx->kc_blocks;
+  if (blocks < 1) blocks = 1;
+  p.part_val = ctx->kc_pp_val;
+  p.part_idx = ctx->kc_pp_idx;
+  void* args[] = {&p};
+  CUDA_TRY(ctx, cudaLaunchCooperativeKernel((const void*)kcenter_persist_kernel<NV>, dim3(blocks), dim3(256), args, 0, st));
+  ctx->launches++;
+  return 0;
+}
+int run_kc_persist(b200al_ctx* ctx, int D, const KcPersistParams& p, cudaStream_t st) {
+  switch (D / 128) {
+    case 1: return launch_kc_persist<1>(ctx, p, st);
+    case 2: return launch_kc_persist<2>(ctx, p, st);
+    case 4: return launch_kc_persist<4>(ctx, p, st);
+    case 8: return launch_kc_persist<8>(ctx, p, st);
+    case 12: return launch_kc_persist<12>(ctx, p, st);
+    case 16: return launch_kc_persist<16>(ctx, p, st);
+  }
+  return set_err(ctx, B200AL_ERR_UNSUPPORTED, "row width %d", D);
+}
+}  // namespace
+
+extern "C" size_t b200al_kcenter_mailbox_bytes(int world) {
+  return world > 0 && world <= kKcMaxWorld ? (size_t)4 * world * sizeof(KcMail) : 0;
+}
+
+extern "C" int b200al_kcenter_run_sharded(b200al_ctx* ctx, const float* d_emb_local, int n_local, int64_t row_base,
+                                          int D, int metric, int criteria, int n_centres, void* d_state,
+                                          uint8_t* d_taken, int budget, int64_t* d_picks, float* d_pick_vals,
+                                          int world, int rank, int epoch, void* d_mail_local,
+                                          void* const* d_mail_peers, const float* const* d_emb_peers,
+                                          const int64_t* row_bases, int timeout_ms, void* stream) {
+  if (!ctx) return set_err(nullptr, B200AL_ERR_ARG, "ctx is NULL");
+  if (budget == 0) return B200AL_OK;
+  if (!d_state || !d_picks || n_local < 0 || budget < 0 || (n_local > 0 && (!d_emb_local || !d_taken)))
+    return set_err(ctx, B200AL_ERR_ARG, "bad argument");
+  if (world < 1 || world > kKcMaxWorld || rank < 0 || rank >= world)
+    return set_err(ctx, B200AL_ERR_ARG, "world %d / rank %d outside [1, %d]", world, rank, kKcMaxWorld);
+  if (world > 1 && (!d_mail_local || !d_mail_peers || !d_emb_peers || !row_bases))
+    return set_err(ctx, B200AL_ERR_ARG, "peer pointers missing");
+  if (epoch < 1 || epoch > 30000) return set_err(ctx, B200AL_ERR_ARG, "epoch must be in [1, 30000]");
+  if (budget > 65000) return set_err(ctx, B200AL_ERR_ARG, "budget above 65000 steps per call");
+  if (metric != B200AL_L2 && metric != B200AL_COSINE) return set_err(ctx, B200AL_ERR_ARG, "bad metric");
+  if (criteria != B200AL_MIN && criteria != B200AL_MEAN) return set_err(ctx, B200AL_ERR_ARG, "bad criteria");
+  if (criteria == B200AL_MEAN && n_centres < 1) return set_err(ctx, B200AL_ERR_ARG, "mean criteria needs n_centres >= 1");
+  if (int rc = check_dim(ctx, D)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  KcPersistParams p;
+  memset(&p, 0, sizeof(p));
+  p.emb = d_emb_local; p.n_local = n_local; p.row_base = row_base;
+  p.metric = metric; p.criteria = criteria; p.n_centres = n_centres; p.budget = budget;
+  p.state = d_state; p.taken = d_taken; p.picks = (long long*)d_picks; p.pick_vals = d_pick_vals;
+  p.world = world; p.rank = rank; p.epoch = epoch;
+  p.mail_local = (KcMail*)d_mail_local;
+  if (world > 1) {
+    for (int r = 0; r < world; ++r) {
+      if (!d_mail_peers[r] || (!d_emb_peers[r] && row_bases[r + 1] > row_bases[r]))
+        return set_err(ctx, B200AL_ERR_ARG, "peer pointer of rank %d is NULL", r);
+      p.mail_peer[r] = (KcMail*)d_mail_peers[r];
+      p.emb_peer[r] = d_emb_peers[r];
+      p.base_peer[r] = row_bases[r];
+    }
+    p.base_peer[world] = row_bases[world];
+    if (row_bases[rank] != row_base || row_bases[rank + 1] - row_bases[rank] != n_local)
+      return set_err(ctx, B200AL_ERR_ARG, "row_bases do not match this rank's shard");
+  }
+  p.timeout_cycles = timeout_ms > 0 ? (long long)timeout_ms * 2000000LL : 0;
+  if (int rc = run_kc_persist(ctx, D, p, st)) return rc;
+  CUDA_TRY(ctx, cudaGetLastError());
+  return B200AL_OK;
+}
+
 extern "C" int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, int D, int metric, int criteria,
                                   int n_centres, void* d_state, uint8_t* d_taken, int budget, int64_t* d_picks,
                                   float* d_pick_vals, void* stream) {
@@ -1580,6 +1666,18 @@ extern "C" int b200al_kcenter_run(b200al_ctx* ctx, const float* d_emb, int n, in
   if (int rc = check_dim(ctx, D)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  if (env_int("B200AL_KC_PERSIST", 1)) {
+    // all `budget` steps in one cooperative launch (kcenter.cuh: kcenter_persist_kernel); same arithmetic, same picks
+    KcPersistParams p;
+    memset(&p, 0, sizeof(p));
+    p.emb = d_emb; p.n_local = n; p.row_base = 0;
+    p.metric = metric; p.criteria = criteria; p.n_centres = n_centres; p.budget = budget;
+    p.state = d_state; p.taken = d_taken; p.picks = (long long*)d_picks; p.pick_vals = d_pick_vals;
+    p.world = 1; p.rank = 0; p.epoch = 1;
+    if (int rc = run_kc_persist(ctx, D, p, st)) return rc;
+    CUDA_TRY(ctx, cudaGetLastError());
+    return B200AL_OK;
+  }
   int blocks = (n + 63) / 64;  // >= 8 rows per warp
   if (blocks > ctx->kc_blocks) blocks = ctx->kc_blocks;
   if (blocks < 1) blocks = 1;

@@ -72,20 +72,31 @@ def main():
             dt, names = timed(lambda: sel.select_next_batch(ad, 32, model, dev))
             out.append({"config": 1, "what": "entropy, K=2, 512-image pool, budget 32", "seconds": dt,
                         "images_per_s": 512 / dt, "selected": len(names)})
-        elif c == "3":
+        elif c in ("3", "3r"):
+            # "3r": embeddings gathered, k-center replicated on every rank (the round-1 design) instead of the sharded
+            # persistent kernel - same picks, for the stage comparison
             model = OracleUNet(golden_state_dict(3, g))
             ad = active(pool_u8(args.pool + 500, dev), 500)
-            sel = b200al.B200CoresetSelector(metric="l2", **kw)
-            dt, names = timed(lambda: sel.select_next_batch(ad, 500, model, dev), reps=1)
-            out.append({"config": 3, "what": f"coreset l2 k-center, K=3, {args.pool}-image pool, 500 labeled, budget 500",
-                        "seconds": dt, "images_per_s": args.pool / dt, "selected": len(set(names))})
+            sel = b200al.B200CoresetSelector(metric="l2", shard_kcenter=(c == "3"), **kw)
+            dt, names = timed(lambda: sel.select_next_batch(ad, 500, model, dev), reps=2)
+            prof = b200al.B200CoresetSelector(metric="l2", shard_kcenter=(c == "3"), profile_stages=True, **kw)
+            prof.select_next_batch(ad, 500, model, dev)
+            import hashlib
+            out.append({"config": c, "what": f"coreset l2 k-center, K=3, {args.pool}-image pool, 500 labeled, budget 500"
+                                             + (" (k-center replicated)" if c == "3r" else ""),
+                        "seconds": dt, "images_per_s": args.pool / dt, "selected": len(set(names)),
+                        "picked_sha16": hashlib.sha256("\n".join(sorted(names)).encode()).hexdigest()[:16],
+                        "stage_seconds_rank0": {k: round(v, 4) for k, v in prof.last_timing["stages"].items()}})
         elif c == "4":
             model = OracleUNet(golden_state_dict(3, g))
             ad = active(pool_u8(args.pool + 500, dev), 500)
             sel = b200al.B200HybridSelector(prefilter_factor=10, **kw)
             dt, names = timed(lambda: sel.select_next_batch(ad, 500, model, dev), reps=1)
+            prof = b200al.B200HybridSelector(prefilter_factor=10, profile_stages=True, **kw)
+            prof.select_next_batch(ad, 500, model, dev)
             out.append({"config": 4, "what": f"hybrid entropy top-5000 -> k-center, K=3, {args.pool}-image pool, budget 500",
-                        "seconds": dt, "images_per_s": args.pool / dt, "selected": len(set(names))})
+                        "seconds": dt, "images_per_s": args.pool / dt, "selected": len(set(names)),
+                        "stage_seconds_rank0": {k: round(v, 4) for k, v in prof.last_timing["stages"].items()}})
         elif c == "k":
             model = OracleUNet(golden_state_dict(3, g))
             ad = active(pool_u8(args.pool + 500, dev), 500)

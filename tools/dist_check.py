@@ -38,6 +38,16 @@ def main():
         np.random.seed(31)
         torch.manual_seed(31)
         out[name] = sel.select_next_batch(make_active(images, 20), 12, model, dev)
+    # k-center variants: under torchrun the default path is the sharded persistent kernel (one candidate per rank and
+    # step over NVLink); `shard_kcenter=False` gathers the rows and runs replicated - all must equal the 1-GPU picks
+    for metric in ("l2", "cosine"):
+        for crit in ("min", "mean"):
+            for shard in (True, False):
+                sel = b200al.B200CoresetSelector(metric=metric, coreset_criteria=crit, shard_kcenter=shard, **kw)
+                out[f"coreset/{metric}/{crit}/{'sharded' if shard else 'replicated'}"] = \
+                    sel.select_next_batch(make_active(images, 20), 40, model, dev)
+    for k in [k for k in out if k.endswith("/sharded")]:
+        assert out[k] == out[k.replace("/sharded", "/replicated")], k
     if rank == 0:
         print(json.dumps(out, indent=0, sort_keys=True))
     if "RANK" in os.environ:
