@@ -53,7 +53,7 @@ def parse():
     ap.add_argument("--pool", type=int, default=POOL, help="images in the (one, sharded) pool")
     ap.add_argument("--chunk", type=int, default=int(os.environ.get("B200AL_CHUNK", 256)),
                     help="samples per forward chunk (256 = 20 GB of activations)")
-    ap.add_argument("--precision", default="bf16x3", choices=["bf16x3", "bf16", "mixed", "mixed-deep"])
+    ap.add_argument("--precision", default="mixed", choices=["mixed", "mixed-deep", "bf16x3", "bf16"])
     ap.add_argument("--cpu-sample", type=int, default=12, help="images in the CPU-baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-config4", action="store_true", help="skip the secondary hybrid 100k record")
@@ -127,7 +127,7 @@ def issue_factor(precision: str) -> float:
 
 def workload_name(args):
     return (f"UNet MC-dropout (T={T_REPEATS}) entropy acquisition, FUGC-shape 1x256x256 K={K_CLASSES}, "
-            f"{args.pool}-image synthetic pool (one pool, sharded across the GPUs), budget {BUDGET}")
+            f"{args.pool}-image synthetic pool of distinct images (one pool, sharded across the GPUs), budget {BUDGET}")
 
 
 def names_hash(names) -> str:
@@ -245,7 +245,8 @@ def run_b200(args):
 
     # ONE pool (every rank builds the same one): image 0 is the labeled set, images 1..n the pool.
     # The selector shards pool positions by contiguous ranges (b200al.dist.shard_range) and reads only its shard.
-    host = synthetic_pool_u8(n + 1).pin_memory()
+    # every pool image is a DISTINCT seeded image (tiled near-duplicates would put near-ties at the cut by construction)
+    host = synthetic_pool_u8(n + 1, distinct=n + 1).pin_memory()
     ad_resident = make_active(host.to(dev), 1)
     ad_host = make_active(host, 1)
     lo, hi = b200al.dist.shard_range(n, rank, world)
@@ -342,7 +343,7 @@ def run_b200(args):
                        "parity": "MC-dropout is a composed oracle: parity unpinned by the reference (SURVEY F6); "
                                  "checked against it at T=8 on the 1000-image prefix (tests/test_gpu_configs.py)",
                        "selection_consistent_resident_vs_e2e": list(picked) == list(picked_e2e),
-                       "picked_sha16": names_hash(picked)},
+                       "picked_set_sha16": names_hash(sorted(picked))},
             "e2e": {"value": n * e2e_steps / (ms_e2e / 1e3), "unit": "images/s", "steps": e2e_steps,
                     "h2d_bytes_per_step": n * 256 * 256, "d2h_bytes_per_step": BUDGET * 12 * world},
             "gpu_launches": int(launches),

@@ -91,7 +91,7 @@ class Engine:
     """One context per (device, K, H, W, max_samples, precision)."""
 
     def __init__(self, device, num_out: int, H: int = 256, W: int = 256, max_samples: int = 64,
-                 precision: str = "bf16x3"):
+                 precision: str = "mixed"):
         self.lib = _lib.load()
         self.device = torch.device(device)
         if self.device.type != "cuda":

@@ -201,7 +201,7 @@ def _timed(fn):
 
 class _B200Base(ActiveSelector):
     def __init__(self, batch_size: int, num_workers: int, pin_memory: bool = True, smooth: float = 1e-8, *,
-                 precision: str = "bf16x3", chunk_samples: int = 64, pool_cache: str = "auto",
+                 precision: str = "mixed", chunk_samples: int = 64, pool_cache: str = "auto",
                  sync_weights: bool = True, profile_stages: bool = False):
         self.batch_size, self.num_workers, self.pin_memory = batch_size, num_workers, pin_memory
         self.smooth = smooth

@@ -25,8 +25,9 @@ def need(cfg, key):
     return cfg[key]
 
 
+@pytest.mark.parametrize("precision", ["mixed", "bf16x3"])
 @pytest.mark.parametrize("mode", ["entropy", "margin", "confidence"])
-def test_config1_512_image_pool_selects_reference_names(cfg, golden, mode):
+def test_config1_512_image_pool_selects_reference_names(cfg, golden, mode, precision):
     """config 1: reference Entropy/Margin/ConfidenceSelector, BUSI-shape K=2, 32 labeled + 512 pool, budget 32."""
     import b200al
     from oracle import select_ref as S
@@ -38,7 +39,7 @@ def test_config1_512_image_pool_selects_reference_names(cfg, golden, mode):
     model = OracleUNet(golden_state_dict(2, golden["model"]))
     cls = {"entropy": b200al.B200EntropySelector, "margin": b200al.B200MarginSelector,
            "confidence": b200al.B200ConfidenceSelector}[mode]
-    sel = cls(batch_size=12, num_workers=0, pin_memory=True, chunk_samples=64)
+    sel = cls(batch_size=12, num_workers=0, pin_memory=True, chunk_samples=64, precision=precision)
     ad = make_active(images, 32)
     got = sel.select_next_batch(ad, 32, model, torch.device(DEV))
     scores, names = sel.cal_scores(ad, model, torch.device(DEV))
@@ -51,7 +52,8 @@ def test_config1_512_image_pool_selects_reference_names(cfg, golden, mode):
     assert len(names) == 512
 
 
-def test_config2_mc_dropout_T8_prefix_matches_composed_oracle(cfg, golden):
+@pytest.mark.parametrize("precision", ["mixed", "bf16x3"])
+def test_config2_mc_dropout_T8_prefix_matches_composed_oracle(cfg, golden, precision):
     """config 2 on the 1000-image prefix SURVEY 8d prescribes: composed MC-dropout oracle at the benchmarked T=8
     (parity unpinned by the reference: MC-dropout does not exist there) - scores and the top-100 names."""
     import b200al
@@ -63,7 +65,8 @@ def test_config2_mc_dropout_T8_prefix_matches_composed_oracle(cfg, golden):
     images = synth_pool_u8(N_LABELED3 + MC_N)[N_LABELED3 - 1:]   # one labeled image + the 1000-image pool prefix
     model = OracleUNet(golden_state_dict(3, golden["model"]))
     sel = b200al.B200MCDropoutEntropySelector(batch_size=32, num_workers=0, pin_memory=True, mc_repeats=MC_T,
-                                              dropout_prob=MC_P, mc_seed=MC_SEED, chunk_samples=256)
+                                              dropout_prob=MC_P, mc_seed=MC_SEED, chunk_samples=256,
+                                              precision=precision)
     ad = make_active(images, 1)
     got = sel.select_next_batch(ad, MC_BUDGET, model, torch.device(DEV))
     scores, _ = sel.cal_scores(ad, model, torch.device(DEV))

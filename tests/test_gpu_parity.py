@@ -12,8 +12,9 @@ LOGIT_ATOL = 2e-2
 DEV = "cuda:0"
 
 
-@pytest.fixture(scope="module")
-def env(golden):
+@pytest.fixture(scope="module", params=["mixed", "bf16x3"])
+def env(golden, request):
+    """Engines in the default per-layer mix and in bf16x3 throughout: every engine-level parity test runs on both."""
     import b200al
     from oracle.synth import synth_pool_u8
     from oracle.unet_ref import OracleUNet, golden_state_dict
@@ -22,7 +23,7 @@ def env(golden):
         g = golden[name]
         n = int(g["n_labeled"]) + int(g["n_pool"])
         sd = golden_state_dict(K, golden["model"])
-        eng = b200al.Engine(DEV, K, max_samples=32)
+        eng = b200al.Engine(DEV, K, max_samples=32, precision=request.param)
         eng.load_model(sd)
         e[K] = dict(g=g, sd=sd, eng=eng, images=synth_pool_u8(n), model=OracleUNet(sd),
                     L=int(g["n_labeled"]), k=int(g["budget"]))

@@ -167,7 +167,7 @@ def main():
     ap.add_argument("--iters", type=int, default=60)
     ap.add_argument("--batch", type=int, default=12)   # the reference CLI's default batch size
     ap.add_argument("--selector", default="b200-entropy")
-    ap.add_argument("--precision", default="bf16x3")
+    ap.add_argument("--precision", default="mixed")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "r02_config5.jsonl"))
     args = ap.parse_args()
     import torch.distributed as dist

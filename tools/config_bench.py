@@ -124,7 +124,7 @@ def main():
             sel = b200al.B200EntropySelector(**kw)
             dt, names = timed(lambda: sel.select_next_batch(ad, 32, model, dev))
             cache = base._b200_pool_cache
-            eng = b200al.selectors.get_engine(dev, 3, 256, 256, "bf16x3", 128)
+            eng = b200al.selectors.get_engine(dev, 3, 256, 256, "mixed", 128)
             rows = torch.arange(32, 32 + 1024, device=dev)
             for _ in range(2):
                 cache.gather(eng, rows)
