@@ -18,7 +18,7 @@ def env(golden, request):
     import b200al
     from oracle.synth import synth_pool_u8
     from oracle.unet_ref import OracleUNet, golden_state_dict
-    e = {}
+    e = {"precision": request.param}
     for K, name in ((2, "pool_K2"), (3, "pool_K3")):
         g = golden[name]
         n = int(g["n_labeled"]) + int(g["n_pool"])
@@ -258,7 +258,7 @@ def test_scores_are_chunk_invariant_and_deterministic(env):
     a = e["eng"].scores(pool, "entropy")
     b = e["eng"].scores(pool, "entropy")
     assert torch.equal(a, b)
-    small = b200al.Engine(DEV, 2, max_samples=5)
+    small = b200al.Engine(DEV, 2, max_samples=5, precision=env["precision"])
     small.load_model(e["sd"])
     c = small.scores(pool, "entropy")
     assert torch.equal(a, c)
