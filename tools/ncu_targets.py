@@ -49,6 +49,12 @@ def main(which):
         uni = np.stack([rs.uniform(size=trials) for _ in range(k - 1)])
         eng.kmeans_pp(X, torch.from_numpy(w), 123, torch.from_numpy(uni), k, trials)
         del X
+    if which == "conv":   # the 23 conv launches of ONE 128-sample chunk in the default (mixed) precision
+        e2 = b200al.Engine(dev, 3, max_samples=128)
+        e2.load_model(StateDictModel(seeded_state_dict(3)))
+        imgs = synthetic_pool_u8(128).to(dev)
+        for _ in range(2):
+            e2.scores(imgs, "entropy")
     if which in ("all", "first"):
         eng.load_model(StateDictModel(seeded_state_dict(3)))
         imgs = synthetic_pool_u8(64).to(dev)
