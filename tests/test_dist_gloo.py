@@ -71,3 +71,40 @@ def test_single_process_passthrough():
     assert D.all_gather_varlen(t) is t
     sd = {"w": torch.ones(2)}
     assert D.broadcast_state_dict(sd, "cpu") is sd
+
+
+def _draws_worker(rank, world, port, out):
+    """Ranks whose RNG states DIFFER (rank-offset seeds) must still agree on the cold-start picks and on the k-means++
+    draws: rank 0's values are broadcast (selectors._cold_start, dist.broadcast_draws); every rank still consumes its
+    own stream, like the single-process reference does."""
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        import b200al
+        from oracle.synth import make_active
+        torch.manual_seed(1000 + rank)
+        np.random.seed(2000 + rank)
+        ad = make_active(torch.zeros(30, 4, 4, dtype=torch.uint8), 0)
+        cold = b200al.B200EntropySelector(4, 0, False).select_next_batch(ad, 6, None, torch.device("cpu"))
+        after_cold = float(torch.rand(1))                     # own stream consumed: differs per rank
+        first = int(np.random.mtrand._rand.choice(30))
+        uni = np.random.mtrand._rand.uniform(size=(5, 3))
+        f2, u2 = D.broadcast_draws(first, uni)
+        ranges = [D.shard_range(101, r, world) for r in range(world)]
+        torch.save({"cold": cold, "after_cold": after_cold, "first": f2, "uni": u2, "own_first": first,
+                    "bcast": D.broadcast_cpu(torch.arange(4) + 10 * rank).tolist(), "ranges": ranges}, f"{out}.{rank}")
+    finally:
+        dist.destroy_process_group()
+
+
+def test_cold_start_and_kmeanspp_draws_agree_across_ranks_world2(tmp_path):
+    out = str(tmp_path / "draws")
+    mp.spawn(_draws_worker, args=(2, 29521, out), nprocs=2, join=True)
+    r0, r1 = torch.load(f"{out}.0", weights_only=False), torch.load(f"{out}.1", weights_only=False)
+    torch.manual_seed(1000)
+    want = [f"{i:06d}" for i in torch.sort(torch.rand(30), descending=True)[1][:6].tolist()]
+    assert r0["cold"] == r1["cold"] == want                   # rank 0's draw, the reference's RNG call sequence
+    assert r0["after_cold"] != r1["after_cold"]
+    assert r0["first"] == r1["first"] == r0["own_first"] and np.array_equal(r0["uni"], r1["uni"])
+    assert r0["bcast"] == r1["bcast"] == [0, 1, 2, 3]
+    assert r0["ranges"] == [(0, 50), (50, 101)]
