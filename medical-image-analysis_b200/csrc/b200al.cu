@@ -304,17 +304,20 @@ ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw, bool pair = false, 
   return nullptr;
 }
 // pair: each CTA of the pair holds half of the weight tile's rows
-int stage_bytes(int bn, int bk, int nsplit, bool pair = false, int mt = 1) {
-  return (nsplit == 3 ? 2 : 1) * (mt * 128 * bk * 2 + (pair ? bn / 2 : bn) * bk * 2);
+// planes: operand planes per pipeline stage - 2 for the bf16 hi/lo pair and for the fp16 layers (two consecutive
+// k-chunks per stage, conv_tc.cuh kKChunks), else 1
+int stage_bytes(int bn, int bk, int planes, bool pair = false, int mt = 1) {
+  return planes * (mt * 128 * bk * 2 + (pair ? bn / 2 : bn) * bk * 2);
 }
 int out_buf_bytes(int cw, int oplanes) { return oplanes * 128 * cw * 2; }
-int conv_smem_bytes(int bn, int bk, int nsplit, int oplanes, int stages, int cw, int nbufs_total, bool pair = false,
+int conv_smem_bytes(int bn, int bk, int planes, int oplanes, int stages, int cw, int nbufs_total, bool pair = false,
                     int mt = 1) {
-  return stages * stage_bytes(bn, bk, nsplit, pair, mt) + nbufs_total * out_buf_bytes(cw, oplanes) + 1024 + 8 * bn * 4;
+  return stages * stage_bytes(bn, bk, planes, pair, mt) + nbufs_total * out_buf_bytes(cw, oplanes) + 1024 + 8 * bn * 4;
 }
 // per-layer operand split and number of output planes (conv_tc.cuh FMT)
 int layer_nsplit(const b200al_ctx* ctx, const Layer& L);
 int layer_oplanes(const b200al_ctx* ctx, const Layer& L);
+int layer_planes(const b200al_ctx* ctx, const Layer& L);
 ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt);
 ConvKernelFn layer_kernel(const b200al_ctx* ctx, const Layer& L);
 int layer_smem(const b200al_ctx* ctx, const Layer& L);
@@ -385,8 +388,8 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
     if (L.bn != 128 && L.bn != 256) L.pair = false, L.bn = n_total < bn_max ? n_total : bn_max;
   }
   // smem policy: small tiles aim for 2 CTAs/SM (<= ~110 KB each), large ones take the whole SM.
-  const int ns = layer_nsplit(ctx, L), opl = layer_oplanes(ctx, L);
-  const int sb = stage_bytes(L.bn, L.bk, ns, L.pair);
+  const int ns = layer_nsplit(ctx, L), opl = layer_oplanes(ctx, L), planes = layer_planes(ctx, L);
+  const int sb = stage_bytes(L.bn, L.bk, planes, L.pair);
   const int kMaxSmem = 227 * 1024;
   const int fixed = 1024 + 8 * L.bn * 4;
   L.cw = (L.bn >= 64 && L.cout >= 64) ? 64 : 32;
@@ -423,7 +426,7 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
     int bk2 = L.bk;
     if (L.bn == 128) bk2 = 32;  // 2 x 128 x 64-channel tiles + a 128-row weight tile leave room for one stage only
     if (L.bn == 64 && env_int("B200AL_MT2_BK", 64) == 32) bk2 = 32;
-    const int sb2 = stage_bytes(L.bn, bk2, ns, false, 2);
+    const int sb2 = stage_bytes(L.bn, bk2, planes, false, 2);
     const int st2 = (kMaxSmem - fixed - 2 * out_buf_bytes(32, opl)) / sb2;
     if (st2 >= 2 && (L.fmt ? pick_kernel_fmt(L.bn, bk2, 32, false, 2, L.fmt) : pick_kernel(L.bn, bk2, ns, 32, false, 2))) {
       L.mt = 2; L.bk = bk2; L.cw = 32; L.ngroups = 2; L.nbuf = 1;
@@ -431,7 +434,9 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
     }
   }
   p.taps = L.kind == KIND_CONV3 ? 9 : 1;
-  p.chunks = L.cin / L.bk;
+  p.chunks = L.cin / (L.bk * (L.fmt >= 2 ? 2 : 1));  // fp16 layers: two BK-channel chunks per pipeline stage
+  if (L.fmt >= 2 && L.cin % (2 * L.bk))
+    return set_err(ctx, B200AL_ERR_UNSUPPORTED, "fp16 layer needs Cin %% %d == 0", 2 * L.bk);
   p.n_total = n_total;
   p.a_lo_off = ib.c_total;
   const int gridW = L.kind == KIND_CONV3 ? outW : inW, gridH = L.kind == KIND_CONV3 ? outH : inH;
@@ -593,6 +598,7 @@ int layer_oplanes(const b200al_ctx* ctx, const Layer& L) {
   if (L.fmt == 0) return layer_nsplit(ctx, L) == 3 ? 2 : 1;
   return L.fmt == 3 ? 2 : 1;
 }
+int layer_planes(const b200al_ctx* ctx, const Layer& L) { return (layer_nsplit(ctx, L) == 3 || L.fmt >= 2) ? 2 : 1; }
 // The format variants are instantiated for the tile shapes the planner gives the layers of the fp16 groups only.
 ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt) {
   if (fmt == 1) {  // bf16x3 operands, fp16 output: the layer in front of a group
@@ -618,7 +624,7 @@ ConvKernelFn layer_kernel(const b200al_ctx* ctx, const Layer& L) {
   return pick_kernel(L.bn, L.bk, layer_nsplit(ctx, L), L.cw, L.pair, L.mt);
 }
 int layer_smem(const b200al_ctx* ctx, const Layer& L) {
-  return conv_smem_bytes(L.bn, L.bk, layer_nsplit(ctx, L), layer_oplanes(ctx, L), L.stages, L.cw, L.nbuf * L.ngroups,
+  return conv_smem_bytes(L.bn, L.bk, layer_planes(ctx, L), layer_oplanes(ctx, L), L.stages, L.cw, L.nbuf * L.ngroups,
                          L.pair, L.mt);
 }
 }  // namespace

@@ -69,8 +69,12 @@ constexpr int kConvThreads = 320;  // TMA warp + MMA warp + 2 epilogue groups of
 // smem: [stages x (A planes, B planes)] [nbuf x planes x 128 x CW staging for the TMA store] [barriers] [affine]
 template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR = false, int MT = 1, int FMT = 0>
 struct ConvTcSmem {
-  static constexpr int kPlanes = (NSPLIT == 3) ? 2 : 1;
-  static constexpr int kOutPlanes = FMT == 0 ? kPlanes : (FMT == 3 ? 2 : 1);
+  // operand planes per pipeline stage: the hi/lo pair (NSPLIT == 3), or - fp16 layers (FMT >= 2) - TWO consecutive
+  // BK-channel chunks, so that one barrier hand-shake feeds 2 x BK/16 MMAs instead of BK/16 (with a single MMA per
+  // k-step the hand-shake latency, not the pipe, bounded these layers: profiles/r02_ncu_full_conv.csv)
+  static constexpr int kKChunks = FMT >= 2 ? 2 : 1;
+  static constexpr int kPlanes = (NSPLIT == 3) ? 2 : kKChunks;
+  static constexpr int kOutPlanes = FMT == 0 ? ((NSPLIT == 3) ? 2 : 1) : (FMT == 3 ? 2 : 1);
   static constexpr int kABytes = 128 * BK * 2;
   static constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * BK * 2;  // rows of B held by this CTA
   static constexpr int kStageBytes = kPlanes * (MT * kABytes + kBBytes);  // [A tile(s): hi, lo per tile][B: hi, lo]
@@ -121,6 +125,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   static_assert(BLOCK_N % CW == 0 && (CW == 32 || CW == 64), "bad store chunk width");
   static_assert(FMT == 0 || (FMT == 1 && NSPLIT == 3) || ((FMT == 2 || FMT == 3) && NSPLIT == 1), "bad operand format");
   constexpr bool A16 = FMT >= 2;              // fp16 operands
+  constexpr bool TWOK = L::kKChunks == 2;     // plane 1 of a stage = the NEXT BK channels (not the lo plane)
   constexpr bool O16 = FMT == 1 || FMT == 2;  // one fp16 output plane
   constexpr int OPL = L::kOutPlanes;
   static_assert(MT == 1 || (MT == 2 && !PAIR && 4 * BLOCK_N <= 512), "super-tiles: two pixel tiles, one CTA");
@@ -195,7 +200,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const int r = tap / 3, s = tap - r * 3;
           mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
           uint8_t* st = smem + (size_t)stage * L::kStageBytes;
-          const int c = p.a_c0[s] + ch * BK;
+          const int c = p.a_c0[s] + ch * BK * L::kKChunks;
+          const int c1 = TWOK ? c + BK : c + p.a_lo_off;  // second plane: next channel chunk, or the lo plane
           const int cx = tc.x0 + p.a_dx[s], cy = tc.y0 + p.a_dy[r], cp = p.a_p[r];
           if (PAIR) {
             // this CTA's pixel tile and its half of the weight tile; all bytes complete on the LEADER's barrier
@@ -204,28 +210,30 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (rank == 0) mbar_arrive_expect_tx(own, 2 * L::kStageBytes);
             else mbar_arrive_remote(fb);
             tma_load_5d_pair(smem_u32(st), &tmA, fb, c, cx, cp, cy, tc.sample);
-            if (NSPLIT == 3) tma_load_5d_pair(smem_u32(st + L::kABytes), &tmA, fb, c + p.a_lo_off, cx, cp, cy, tc.sample);
+            if (L::kPlanes == 2) tma_load_5d_pair(smem_u32(st + L::kABytes), &tmA, fb, c1, cx, cp, cy, tc.sample);
             for (int pl = 0; pl < L::kPlanes; ++pl)
-              tma_load_2d_pair(smem_u32(st + L::kPlanes * L::kABytes + pl * L::kBBytes), &tmB, fb, ch * BK,
-                               (pl * p.taps + tap) * p.n_total + tc.n0 + (int)rank * (BLOCK_N / 2));
+              tma_load_2d_pair(smem_u32(st + L::kPlanes * L::kABytes + pl * L::kBBytes), &tmB, fb,
+                               TWOK ? (ch * 2 + pl) * BK : ch * BK,
+                               ((TWOK ? 0 : pl) * p.taps + tap) * p.n_total + tc.n0 + (int)rank * (BLOCK_N / 2));
           } else {
             const uint32_t fb = smem_u32(&full_bar[stage]);
             mbar_arrive_expect_tx(fb, L::kStageBytes);
             tma_load_5d(smem_u32(st), &tmA, fb, c, cx, cp, cy, tc.sample);
-            if (NSPLIT == 3) tma_load_5d(smem_u32(st + L::kABytes), &tmA, fb, c + p.a_lo_off, cx, cp, cy, tc.sample);
+            if (L::kPlanes == 2) tma_load_5d(smem_u32(st + L::kABytes), &tmA, fb, c1, cx, cp, cy, tc.sample);
             if (MT == 2) {  // second pixel tile of the super-tile
               uint8_t* st1 = st + L::kPlanes * L::kABytes;
               const int cx1 = tc1.x0 + p.a_dx[s], cy1 = tc1.y0 + p.a_dy[r];
               tma_load_5d(smem_u32(st1), &tmA, fb, c, cx1, cp, cy1, tc1.sample);
-              if (NSPLIT == 3)
-                tma_load_5d(smem_u32(st1 + L::kABytes), &tmA, fb, c + p.a_lo_off, cx1, cp, cy1, tc1.sample);
+              if (L::kPlanes == 2)
+                tma_load_5d(smem_u32(st1 + L::kABytes), &tmA, fb, c1, cx1, cp, cy1, tc1.sample);
             }
             // the weight tile is fetched as two boxes of BLOCK_N/2 rows per plane (one tensor map serves both modes)
             for (int pl = 0; pl < L::kPlanes; ++pl) {
               uint8_t* bdst = st + MT * L::kPlanes * L::kABytes + pl * L::kBBytes;
-              const int row = (pl * p.taps + tap) * p.n_total + tc.n0;
-              tma_load_2d(smem_u32(bdst), &tmB, fb, ch * BK, row);
-              tma_load_2d(smem_u32(bdst + L::kBBytes / 2), &tmB, fb, ch * BK, row + BLOCK_N / 2);
+              const int row = ((TWOK ? 0 : pl) * p.taps + tap) * p.n_total + tc.n0;
+              const int col = TWOK ? (ch * 2 + pl) * BK : ch * BK;
+              tma_load_2d(smem_u32(bdst), &tmB, fb, col, row);
+              tma_load_2d(smem_u32(bdst + L::kBBytes / 2), &tmB, fb, col, row + BLOCK_N / 2);
             }
           }
           if (++stage == stages) { stage = 0; phase ^= 1; }
@@ -263,6 +271,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               const uint32_t accum = (kb > 0 || k > 0) ? 1u : 0u;
               if (PAIR) {
                 umma_bf16_pair(d_tmem, da, db, idesc, accum);
+                if (TWOK) umma_bf16_pair(d_tmem, make_desc(a_lo + 2 * k, kDescHi), make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
                 if (NSPLIT == 3) {
                   umma_bf16_pair(d_tmem, da, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
                   umma_bf16_pair(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
@@ -278,6 +287,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                 }
               } else {
                 umma_bf16(d_tmem, da, db, idesc, accum);
+                if (TWOK) umma_bf16(d_tmem, make_desc(a_lo + 2 * k, kDescHi), make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
                 if (NSPLIT == 3) {
                   umma_bf16(d_tmem, da, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
                   umma_bf16(d_tmem, make_desc(a_lo + 2 * k, kDescHi), db, idesc, 1u);
@@ -286,6 +296,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
                   constexpr uint32_t kA1 = (L::kPlanes * L::kABytes) >> 4;
                   const uint64_t da1 = make_desc(a_hi + kA1 + 2 * k, kDescHi);
                   umma_bf16(d_tmem + BLOCK_N, da1, db, idesc, accum);
+                  if (TWOK)
+                    umma_bf16(d_tmem + BLOCK_N, make_desc(a_lo + kA1 + 2 * k, kDescHi), make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
                   if (NSPLIT == 3) {
                     umma_bf16(d_tmem + BLOCK_N, da1, make_desc(b_lo + 2 * k, kDescHi), idesc, 1u);
                     umma_bf16(d_tmem + BLOCK_N, make_desc(a_lo + kA1 + 2 * k, kDescHi), db, idesc, 1u);
