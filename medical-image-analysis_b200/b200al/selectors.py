@@ -434,8 +434,12 @@ class B200CoresetSelector(_B200Base):
         and reading the chosen centre from its owner's shard over NVLink (csrc/kcenter.cuh, kcenter_persist_kernel).
         Global rows: 0..L-1 labeled (coreset_selector.py:85-88), L + p = pool position p."""
         self._stages.start("kcenter")
-        _require_finite(emb_l, "embeddings")
-        _require_finite(emb_local, "embeddings")
+        # collective check: a NaN in ONE shard must make every rank raise (not leave the others waiting at the barrier)
+        ok = torch.tensor([float(bool(torch.isfinite(emb_l).all()) and bool(torch.isfinite(emb_local).all()))],
+                          device=eng.device)
+        torch.distributed.all_reduce(ok, op=torch.distributed.ReduceOp.MIN)
+        if not bool(ok.item()):
+            raise RuntimeError("non-finite values in the embeddings: the selection would be arbitrary")
         if self.metric == "cosine":
             emb_l, emb_local = eng.normalize_rows(emb_l), eng.normalize_rows(emb_local)
         bases = [labeled_size + D.shard_range(pool_size, r, ws)[0] for r in range(ws)] + [labeled_size + pool_size]
