@@ -239,6 +239,8 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
+        # NCCL writes its version banner to stdout; stdout carries the ONE JSON line, so send NCCL's log to stderr
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     n = args.pool
     model = StateDictModel(seeded_state_dict(K_CLASSES), dropout_p=DROP_P)
