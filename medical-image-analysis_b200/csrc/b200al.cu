@@ -935,16 +935,19 @@ int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, const float
   const ActBuf& ob = ctx->bufs[E0A];
   const size_t smem = (size_t)T * 64 * sizeof(float);
   if (smem > 48 * 1024) return set_err(ctx, B200AL_ERR_ARG, "T = %d too large", T);
-  if (dtype == B200AL_U8)
-    conv_first_kernel<uint8_t><<<grid, 256, smem, st>>>((const uint8_t*)d_images, norm, T, ctx->H, ctx->W,
-                                                       ctx->first_consts, mask, B200AL_MASK_CHANNELS, ctx->slope,
-                                                       ob.ptr, 2 * ob.c_total, 0, ob.c_total, ctx->nsplit == 3);
-  else if (dtype == B200AL_F32)
-    conv_first_kernel<float><<<grid, 256, smem, st>>>((const float*)d_images, norm, T, ctx->H, ctx->W,
-                                                     ctx->first_consts, mask, B200AL_MASK_CHANNELS, ctx->slope, ob.ptr,
-                                                     2 * ob.c_total, 0, ob.c_total, ctx->nsplit == 3);
-  else
+  const bool unit = ctx->slope >= 0.f && ctx->slope <= 1.f;
+#define B200AL_FIRST(IMG, UNIT)                                                                                     \
+  conv_first_kernel<IMG, UNIT><<<grid, 256, smem, st>>>((const IMG*)d_images, norm, T, ctx->H, ctx->W,              \
+                                                        ctx->first_consts, mask, B200AL_MASK_CHANNELS, ctx->slope, \
+                                                        ob.ptr, 2 * ob.c_total, 0, ob.c_total, ctx->nsplit == 3)
+  if (dtype == B200AL_U8) {
+    if (unit) B200AL_FIRST(uint8_t, true); else B200AL_FIRST(uint8_t, false);
+  } else if (dtype == B200AL_F32) {
+    if (unit) B200AL_FIRST(float, true); else B200AL_FIRST(float, false);
+  } else {
     return set_err(ctx, B200AL_ERR_ARG, "bad image dtype %d", dtype);
+  }
+#undef B200AL_FIRST
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   return 0;

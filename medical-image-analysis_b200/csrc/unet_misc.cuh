@@ -116,13 +116,21 @@ struct FirstConvConsts {
   float bias[32], scale[32], shift[32];
 };
 
-template <typename ImgT>
-__global__ void __launch_bounds__(256)
+// two fp32 values -> packed bf16x2 (a in the low half), round to nearest even: one F2FP instead of two F2F + a PRMT
+__device__ __forceinline__ uint32_t cvt_bf16x2_rn(float a, float b) {
+  uint32_t r;
+  asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+  return r;
+}
+
+// UNIT_SLOPE: 0 <= slope <= 1 (the reference's 0.01, blocks.py:100), where leaky(y) == max(y, slope * y)
+template <typename ImgT, bool UNIT_SLOPE>
+__global__ void __launch_bounds__(256, 3)
 conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, int T, int H, int W,
                   const __grid_constant__ FirstConvConsts k,
                   const float* __restrict__ mask, int mask_stride, float slope, __nv_bfloat16* __restrict__ out,
                   int out_pitch, int hi_off, int lo_off, int write_lo) {
-  extern __shared__ float se[];  // [T][32] scale, then [T][32] shift
+  extern __shared__ __align__(16) float se[];  // [T][32] scale, then [T][32] shift
   float* ses = se;
   float* seh = se + T * 32;
   const int im_idx = blockIdx.z;
@@ -133,6 +141,19 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
     ses[i] = sc;
     seh[i] = k.bias[c] * sc + k.shift[c];
   }
+  // ZScoreNormalize fused into the loader (normalization.py:21): (x - mean) / std on real pixels, padding stays 0
+  const float nm = norm ? norm[2 * im_idx] : 0.f;
+  const float nsd = norm ? norm[2 * im_idx + 1] : 1.f;
+  // 8-bit pixels: torchvision to_tensor (x / 255, an IEEE division) and the z-score division, once per byte value
+  // and block instead of nine times per pixel
+  __shared__ float lut[256];
+  if (sizeof(ImgT) == 1) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
+      float t = (float)i / 255.0f;
+      if (norm) t = __fdiv_rn(t - nm, nsd);
+      lut[i] = t;
+    }
+  }
   __syncthreads();
   // every store instruction of a warp must cover contiguous bytes (a lane-strided 16-byte store costs
   // one L1 wavefront per lane): the 32 pixels x 128 B of a warp are transposed through shared memory
@@ -142,9 +163,6 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
   const int x0w = x - lane;
   const int y = blockIdx.y;
   const ImgT* im = img + (size_t)im_idx * H * W;
-  // ZScoreNormalize fused into the loader (normalization.py:21): (x - mean) / std on real pixels, padding stays 0
-  const float nm = norm ? norm[2 * im_idx] : 0.f;
-  const float nsd = norm ? norm[2 * im_idx + 1] : 1.f;
   float v[9];
 #pragma unroll
   for (int r = 0; r < 3; ++r)
@@ -153,9 +171,12 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
       const int yy = y + r - 1, xx = x + c - 1;
       float t = 0.f;
       if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-        if (sizeof(ImgT) == 1) t = (float)im[(size_t)yy * W + xx] / 255.0f;  // torchvision to_tensor
-        else t = (float)im[(size_t)yy * W + xx];
-        if (norm) t = __fdiv_rn(t - nm, nsd);
+        if (sizeof(ImgT) == 1) {
+          t = lut[(int)im[(size_t)yy * W + xx]];
+        } else {
+          t = (float)im[(size_t)yy * W + xx];
+          if (norm) t = __fdiv_rn(t - nm, nsd);
+        }
       }
       v[r * 3 + c] = t;
     }
@@ -171,24 +192,28 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
   for (int t = 0; t < T; ++t) {
     const float* sc = ses + t * 32;
     const float* sh = seh + t * 32;
-    uint32_t hi[16], lo[16];
+    __syncwarp();  // the previous repeat's reads of ws are done
 #pragma unroll
-    for (int co = 0; co < 32; co += 2) {
-      const float2 s2 = *reinterpret_cast<const float2*>(sc + co);
-      const float2 h2 = *reinterpret_cast<const float2*>(sh + co);
-      const float a0 = leaky(acc[co] * s2.x + h2.x, slope);
-      const float a1 = leaky(acc[co + 1] * s2.y + h2.y, slope);
-      __nv_bfloat16 h0, l0, h1, l1;
-      split_bf16(a0, h0, l0);
-      split_bf16(a1, h1, l1);
-      hi[co / 2] = pack_bf16x2(h0, h1);
-      lo[co / 2] = pack_bf16x2(l0, l1);
-    }
-    __syncwarp();
+    for (int g = 0; g < 4; ++g) {  // 8 channels at a time: one 16-byte hi word and one lo word per pixel
+      uint32_t hi[4], lo[4];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      ws[lane * 8 + (j ^ (lane & 7))] = make_uint4(hi[4 * j], hi[4 * j + 1], hi[4 * j + 2], hi[4 * j + 3]);
-      ws[lane * 8 + ((4 + j) ^ (lane & 7))] = make_uint4(lo[4 * j], lo[4 * j + 1], lo[4 * j + 2], lo[4 * j + 3]);
+      for (int q = 0; q < 2; ++q) {
+        const int co = g * 8 + q * 4;
+        const float4 s4 = *reinterpret_cast<const float4*>(sc + co);
+        const float4 h4 = *reinterpret_cast<const float4*>(sh + co);
+        float a[4] = {fmaf(acc[co], s4.x, h4.x), fmaf(acc[co + 1], s4.y, h4.y), fmaf(acc[co + 2], s4.z, h4.z),
+                      fmaf(acc[co + 3], s4.w, h4.w)};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) a[j] = UNIT_SLOPE ? fmaxf(a[j], a[j] * slope) : leaky(a[j], slope);
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          const uint32_t h = cvt_bf16x2_rn(a[2 * j], a[2 * j + 1]);
+          hi[q * 2 + j] = h;
+          lo[q * 2 + j] = cvt_bf16x2_rn(a[2 * j] - bf16lo_to_float(h), a[2 * j + 1] - bf16hi_to_float(h));
+        }
+      }
+      ws[lane * 8 + (g ^ (lane & 7))] = make_uint4(hi[0], hi[1], hi[2], hi[3]);
+      ws[lane * 8 + ((4 + g) ^ (lane & 7))] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
     }
     __syncwarp();
     __nv_bfloat16* dstw = out + ((size_t)((size_t)(im_idx * T + t) * H + y) * W + x0w) * out_pitch;
