@@ -51,7 +51,21 @@ def main():
         ms, launches, flops = eng.conv_time_ms()
         per = [t * 1e3 / (args.reps * args.samples) for t in eng.layer_times_ms()]   # us per sample
         eng.set_timing(False)
-        rec = {"precision": prec, "samples": args.samples, "max_abs_logit_err_vs_reference": logit_err,
+
+        def whole(fn):   # us per sample of the whole call (first conv, conv layers, reduction), CUDA events
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            fn()
+            e0.record()
+            for _ in range(args.reps):
+                fn()
+            e1.record()
+            torch.cuda.synchronize()
+            return round(e0.elapsed_time(e1) * 1e3 / (args.reps * args.samples), 2)
+
+        total_scores = whole(lambda: eng.scores(big, "entropy"))
+        total_embed = whole(lambda: eng.embed(big))
+        rec = {"precision": prec, "samples": args.samples, "scores_call_us_per_sample": total_scores,
+               "embed_call_us_per_sample": total_embed, "max_abs_logit_err_vs_reference": logit_err,
                "max_rel_score_err_vs_reference": rel, "conv_us_per_sample": round(sum(per), 2),
                "conv_tflops_algorithmic": round(flops / (ms / 1e3) / 1e12, 1),
                "layers": {nm: {"us_per_sample": round(t, 3), "tflops": round(gf * 1e9 / (t * 1e-6) / 1e12, 1) if t > 0 else None}
