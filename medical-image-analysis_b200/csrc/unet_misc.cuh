@@ -134,7 +134,8 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
   float* ses = se;
   float* seh = se + T * 32;
   const int im_idx = blockIdx.z;
-  for (int i = threadIdx.x; i < T * 32; i += blockDim.x) {
+  // launched with 256 threads (run_first_conv)
+  for (int i = threadIdx.x; i < T * 32; i += 256) {
     const int t = i >> 5, c = i & 31;
     float sc = k.scale[c];
     if (mask) sc *= mask[(size_t)(im_idx * T + t) * mask_stride + c];
@@ -147,12 +148,12 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
   // 8-bit pixels: torchvision to_tensor (x / 255, an IEEE division) and the z-score division, once per byte value
   // and block instead of nine times per pixel
   __shared__ float lut[256];
+  __shared__ __align__(16) float wsm[288];
+  for (int i = threadIdx.x; i < 288; i += 256) wsm[i] = k.w[i];
   if (sizeof(ImgT) == 1) {
-    for (int i = threadIdx.x; i < 256; i += blockDim.x) {
-      float t = (float)i / 255.0f;
-      if (norm) t = __fdiv_rn(t - nm, nsd);
-      lut[i] = t;
-    }
+    float t = (float)threadIdx.x / 255.0f;
+    if (norm) t = __fdiv_rn(t - nm, nsd);
+    lut[threadIdx.x] = t;
   }
   __syncthreads();
   // every store instruction of a warp must cover contiguous bytes (a lane-strided 16-byte store costs
@@ -164,29 +165,42 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
   const int y = blockIdx.y;
   const ImgT* im = img + (size_t)im_idx * H * W;
   float v[9];
+  // taps: clamped unconditional loads, padding selected to 0 afterwards (no divergent regions)
 #pragma unroll
-  for (int r = 0; r < 3; ++r)
+  for (int r = 0; r < 3; ++r) {
+    const int yy = y + r - 1;
+    const bool rok = (unsigned)yy < (unsigned)H;
+    const ImgT* row = im + (size_t)min(max(yy, 0), H - 1) * W;
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      const int yy = y + r - 1, xx = x + c - 1;
-      float t = 0.f;
-      if (yy >= 0 && yy < H && xx >= 0 && xx < W) {
-        if (sizeof(ImgT) == 1) {
-          t = lut[(int)im[(size_t)yy * W + xx]];
-        } else {
-          t = (float)im[(size_t)yy * W + xx];
-          if (norm) t = __fdiv_rn(t - nm, nsd);
-        }
+      const int xx = x + c - 1;
+      const bool ok = rok && (unsigned)xx < (unsigned)W;
+      const ImgT raw = row[min(max(xx, 0), W - 1)];
+      float t;
+      if (sizeof(ImgT) == 1) {
+        t = lut[(int)raw];
+      } else {
+        t = (float)raw;
+        if (norm) t = __fdiv_rn(t - nm, nsd);
       }
-      v[r * 3 + c] = t;
+      v[r * 3 + c] = ok ? t : 0.f;
     }
+  }
+  // weights from shared memory, four per broadcast load: as kernel-parameter operands the 288 weights went through
+  // uniform registers and cost about one extra instruction per FFMA in moves and refills
   float acc[32];
 #pragma unroll
-  for (int co = 0; co < 32; ++co) {
-    float a = 0.f;
+  for (int co = 0; co < 32; ++co) acc[co] = 0.f;
+  const float4* w4 = reinterpret_cast<const float4*>(wsm);
 #pragma unroll
-    for (int kk = 0; kk < 9; ++kk) a = fmaf(v[kk], k.w[co * 9 + kk], a);
-    acc[co] = a;
+  for (int q = 0; q < 72; ++q) {
+    const float4 w = w4[q];
+    const float we[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int e = 4 * q + j;  // = co * 9 + tap, taps of a channel in ascending order as before
+      acc[e / 9] = fmaf(v[e % 9], we[j], acc[e / 9]);
+    }
   }
   uint4* ws = stg[warp];
   for (int t = 0; t < T; ++t) {
@@ -216,15 +230,25 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
       ws[lane * 8 + ((4 + g) ^ (lane & 7))] = make_uint4(lo[0], lo[1], lo[2], lo[3]);
     }
     __syncwarp();
-    __nv_bfloat16* dstw = out + ((size_t)((size_t)(im_idx * T + t) * H + y) * W + x0w) * out_pitch;
+    // lane -> (pixel lane >> 3 of each group of 4, 16-byte column c of the pixel's 128 B); 8 stores, 4 pixels apart
     const int c = lane & 7;
+    __nv_bfloat16* d = out + ((size_t)((size_t)(im_idx * T + t) * H + y) * W + x0w + (lane >> 3)) * out_pitch +
+                       (c < 4 ? hi_off + c * 8 : lo_off + (c - 4) * 8);
+    const bool col_on = c < 4 || write_lo;
+    const uint4* wsr = ws + (lane >> 3) * 8;
+    if (x0w + 32 <= W) {  // whole warp inside the row (always, when W is a multiple of 32)
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int px = i * 4 + (lane >> 3);
-      const uint4 val = ws[px * 8 + (c ^ (px & 7))];
-      if (x0w + px < W && (c < 4 || write_lo)) {
-        __nv_bfloat16* d = dstw + (size_t)px * out_pitch + (c < 4 ? hi_off + c * 8 : lo_off + (c - 4) * 8);
-        *reinterpret_cast<uint4*>(d) = val;
+      for (int i = 0; i < 8; ++i) {
+        const int px = i * 4 + (lane >> 3);
+        const uint4 val = wsr[i * 32 + (c ^ (px & 7))];
+        if (col_on) *reinterpret_cast<uint4*>(d + (size_t)i * 4 * out_pitch) = val;
+      }
+    } else {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int px = i * 4 + (lane >> 3);
+        const uint4 val = wsr[i * 32 + (c ^ (px & 7))];
+        if (x0w + px < W && col_on) *reinterpret_cast<uint4*>(d + (size_t)i * 4 * out_pitch) = val;
       }
     }
   }
@@ -237,7 +261,20 @@ __global__ void avgpool_kernel(const __nv_bfloat16* __restrict__ act, int hw, in
   for (int c = threadIdx.x; c < c_total; c += blockDim.x) {
     const __nv_bfloat16* base = act + (size_t)s * hw * pitch + c;
     float acc = 0.f;
-    for (int i = 0; i < hw; ++i) {
+    int i = 0;
+    // same pixel-order sum as the plain loop below (bit-identical), with 16 pixels' loads in flight at a time: the
+    // kernel is bound by load latency (one block per sample, 256 dependent steps), not by bytes
+    for (; i + 16 <= hw; i += 16) {
+      float vh[16], vl[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        vh[j] = __bfloat162float(base[(size_t)(i + j) * pitch + hi_off]);
+        vl[j] = use_lo ? __bfloat162float(base[(size_t)(i + j) * pitch + lo_off]) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 16; ++j) acc += use_lo ? vh[j] + vl[j] : vh[j];
+    }
+    for (; i < hw; ++i) {
       float v = __bfloat162float(base[(size_t)i * pitch + hi_off]);
       if (use_lo) v += __bfloat162float(base[(size_t)i * pitch + lo_off]);
       acc += v;
