@@ -931,7 +931,10 @@ namespace {
 // norm nullable [n][2] = per-image (mean, std) of the fused ZScoreNormalize
 int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, const float* norm, int n, int T, const float* mask,
                    cudaStream_t st) {
-  dim3 grid((ctx->W + 255) / 256, ctx->H, n);
+  // rows per block (sliding 3x3 window, one set-up per block): as many as leave >= 8 waves of 3 blocks per SM
+  int rows = 8;
+  while (rows > 1 && (long long)((ctx->H + rows - 1) / rows) * n < 8LL * 3 * ctx->sm_count) rows >>= 1;
+  dim3 grid((ctx->W + 255) / 256, (ctx->H + rows - 1) / rows, n);
   const ActBuf& ob = ctx->bufs[E0A];
   const size_t smem = (size_t)T * 64 * sizeof(float);
   if (smem > 48 * 1024) return set_err(ctx, B200AL_ERR_ARG, "T = %d too large", T);
@@ -939,7 +942,7 @@ int run_first_conv(b200al_ctx* ctx, const void* d_images, int dtype, const float
 #define B200AL_FIRST(IMG, UNIT)                                                                                     \
   conv_first_kernel<IMG, UNIT><<<grid, 256, smem, st>>>((const IMG*)d_images, norm, T, ctx->H, ctx->W,              \
                                                         ctx->first_consts, mask, B200AL_MASK_CHANNELS, ctx->slope, \
-                                                        ob.ptr, 2 * ob.c_total, 0, ob.c_total, ctx->nsplit == 3)
+                                                        ob.ptr, 2 * ob.c_total, 0, ob.c_total, ctx->nsplit == 3, rows)
   if (dtype == B200AL_U8) {
     if (unit) B200AL_FIRST(uint8_t, true); else B200AL_FIRST(uint8_t, false);
   } else if (dtype == B200AL_F32) {

@@ -129,7 +129,7 @@ __global__ void __launch_bounds__(256, 3)
 conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, int T, int H, int W,
                   const __grid_constant__ FirstConvConsts k,
                   const float* __restrict__ mask, int mask_stride, float slope, __nv_bfloat16* __restrict__ out,
-                  int out_pitch, int hi_off, int lo_off, int write_lo) {
+                  int out_pitch, int hi_off, int lo_off, int write_lo, int rows) {
   extern __shared__ __align__(16) float se[];  // [T][32] scale, then [T][32] shift
   float* ses = se;
   float* seh = se + T * 32;
@@ -162,30 +162,55 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int x = blockIdx.x * blockDim.x + threadIdx.x;
   const int x0w = x - lane;
-  const int y = blockIdx.y;
   const ImgT* im = img + (size_t)im_idx * H * W;
-  float v[9];
-  // taps: clamped unconditional loads, padding selected to 0 afterwards (no divergent regions)
+  // A block walks `rows` consecutive image rows: the 3x3 window slides down (three new taps per row instead of
+  // nine), the lookup table / weights / scales are set up once, and the next row's bytes are in flight while this
+  // row is computed and stored.  Taps are clamped unconditional loads, padding is selected to 0 afterwards.
+  int xc[3];
+  bool cok[3];
 #pragma unroll
-  for (int r = 0; r < 3; ++r) {
-    const int yy = y + r - 1;
-    const bool rok = (unsigned)yy < (unsigned)H;
+  for (int c = 0; c < 3; ++c) {
+    const int xx = x + c - 1;
+    cok[c] = (unsigned)xx < (unsigned)W;
+    xc[c] = min(max(xx, 0), W - 1);
+  }
+  auto fetch = [&](int yy, ImgT* raw) {
     const ImgT* row = im + (size_t)min(max(yy, 0), H - 1) * W;
 #pragma unroll
+    for (int c = 0; c < 3; ++c) raw[c] = row[xc[c]];
+  };
+  auto taps = [&](int yy, const ImgT* raw, float* dst) {
+    const bool rok = (unsigned)yy < (unsigned)H;
+#pragma unroll
     for (int c = 0; c < 3; ++c) {
-      const int xx = x + c - 1;
-      const bool ok = rok && (unsigned)xx < (unsigned)W;
-      const ImgT raw = row[min(max(xx, 0), W - 1)];
       float t;
       if (sizeof(ImgT) == 1) {
-        t = lut[(int)raw];
+        t = lut[(int)raw[c]];
       } else {
-        t = (float)raw;
+        t = (float)raw[c];
         if (norm) t = __fdiv_rn(t - nm, nsd);
       }
-      v[r * 3 + c] = ok ? t : 0.f;
+      dst[c] = (rok && cok[c]) ? t : 0.f;
     }
+  };
+  const int y0 = blockIdx.y * rows;
+  const int y1 = min(y0 + rows, H);
+  float v[9];
+  ImgT raw[3];
+  fetch(y0 - 1, raw);
+  taps(y0 - 1, raw, v + 3);
+  fetch(y0, raw);
+  taps(y0, raw, v + 6);
+  fetch(y0 + 1, raw);
+  uint4* ws = stg[warp];
+  for (int y = y0; y < y1; ++y) {
+#pragma unroll
+  for (int c = 0; c < 3; ++c) {
+    v[c] = v[3 + c];
+    v[3 + c] = v[6 + c];
   }
+  taps(y + 1, raw, v + 6);
+  fetch(y + 2, raw);  // for the next row
   // weights from shared memory, four per broadcast load: as kernel-parameter operands the 288 weights went through
   // uniform registers and cost about one extra instruction per FFMA in moves and refills
   float acc[32];
@@ -202,7 +227,6 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
       acc[e / 9] = fmaf(v[e % 9], we[j], acc[e / 9]);
     }
   }
-  uint4* ws = stg[warp];
   for (int t = 0; t < T; ++t) {
     const float* sc = ses + t * 32;
     const float* sh = seh + t * 32;
@@ -252,6 +276,7 @@ conv_first_kernel(const ImgT* __restrict__ img, const float* __restrict__ norm, 
       }
     }
   }
+  }  // rows
 }
 
 // Bottleneck global average pool (unet.py:92): [S, HW, pitch] hi/lo -> [S, C] fp32.
