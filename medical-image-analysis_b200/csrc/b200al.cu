@@ -422,7 +422,9 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   const int mt2 = env_int("B200AL_MT2", 3);
   // (not for Cin >= 256: those k-loops are long enough to be MMA-bound already and lose with the smaller BK)
   if (mt2 && L.kind == KIND_CONV3 && !L.pair && L.cin <= 128 && L.bn >= 64 && L.bn <= 128 &&
-      (mt2 & (L.bn == 64 ? 1 : 2))) {
+      (mt2 & (L.bn == 64 ? 1 : 2)) && !(L.fmt == 2 && L.bn == 128 && !env_int("B200AL_MT2_F16", 0))) {
+    // (fp16 128 -> 128 layers: the single 128 x 64-channel x 2-chunk tile measured 1.46 -> 1.33 us per sample against
+    // the super-tile with 32-channel chunks: longer stages matter more than the shared weight tile there)
     int bk2 = L.bk;
     if (L.bn == 128) bk2 = 32;  // 2 x 128 x 64-channel tiles + a 128-row weight tile leave room for one stage only
     if (L.bn == 64 && env_int("B200AL_MT2_BK", 64) == 32) bk2 = 32;
