@@ -182,14 +182,14 @@ def run_reference(args):
     cb = {"value": v, "unit": "images/s", "cores": os.cpu_count(), "kind": "port",
           "sample": f"{per_step} images x T={T_REPEATS} per step (oracle port of the reference path, torch fp32 CPU; "
                     "MC-dropout does not exist in the reference, so the port composes its UNet + Dropout2d + entropy)"}
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": v, "unit": "images/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args), "note": "CPU host cores; each step is a bounded sample"},
         "cpu_baseline": cb,
         "e2e": {"value": v, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def ncu_traffic():
@@ -239,8 +239,6 @@ def run_b200(args):
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
     if world > 1:
-        # NCCL writes its version banner to stdout; stdout carries the ONE JSON line, so send NCCL's log to stderr
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
         dist.init_process_group("nccl", device_id=dev)
     n = args.pool
     model = StateDictModel(seeded_state_dict(K_CLASSES), dropout_p=DROP_P)
@@ -378,7 +376,7 @@ def run_b200(args):
             line["config4"] = c4
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = cpu_baseline(args.cpu_sample)
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
 
@@ -412,8 +410,23 @@ def run_config4(args, dev, rank, world, timed):
             "stage_note": "separate profiled call (device synchronised at stage boundaries)"}
 
 
+def _claim_stdout():
+    """stdout carries exactly ONE JSON line, but libraries write there too (NCCL prints its version banner to fd 1
+    whatever NCCL_DEBUG_FILE says).  Keep the real stdout for the result and point fd 1 at stderr for everyone else."""
+    global _RESULT_OUT
+    sys.stdout.flush()
+    _RESULT_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    _RESULT_OUT.write(json.dumps(line) + "\n")
+    _RESULT_OUT.flush()
+
+
 if __name__ == "__main__":
     a = parse()
+    _claim_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
