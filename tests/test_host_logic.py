@@ -237,3 +237,23 @@ def test_pool_source_serves_cached_rows_in_pool_order():
 def test_conv_flops_match_survey():
     assert abs(b200al.conv_flops_per_sample() / 1e9 - (24.071 - 0.038 - 0.008)) < 0.02   # minus first conv and head
     assert abs(b200al.conv_flops_per_sample(encoder_only=True) / 1e9 - (8.493 - 0.038)) < 0.01
+
+
+def test_bench_reference_arm_prints_exactly_one_json_line():
+    """bench.py's contract: stdout is ONE JSON line (libraries that write to fd 1 are pointed at stderr).  The
+    reference arm runs on the CPU, so it can be checked here; the keys are the ones the driver reads."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "bench.py"), "--impl", "reference", "--steps", "1",
+                        "--warmup", "0", "--cpu-sample", "1"], capture_output=True, text=True, timeout=600, cwd=root)
+    assert r.returncode == 0, r.stderr[-2000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, r.stdout
+    line = json.loads(lines[0])
+    assert line["impl"] == "reference" and line["unit"] == "images/s" and line["higher_is_better"] is True
+    assert line["value"] > 0 and line["steps"] == 1 and line["n_gpus"] == 1
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
+    assert "workload" in line["config"]
