@@ -291,18 +291,92 @@ def stage_select():
     np.savez(tmp("select.npz"), **out)
 
 
+KM_SEED = 4242
+
+
+def stage_kmean():
+    """KMeanSelector at config-3 scale: the reference's own select_next_batch VERBATIM (its
+    DataLoaders - pool first, then labeled, kmean_selector.py:146-156 -, row standardisation, sklearn
+    pairwise_distances + kmeans_plusplus on numpy's global RNG) over the cached reference embeddings of the 20 500
+    images, cosine (its default metric) and l2; frozen: the selected names, the reference's and the oracle's pick
+    order, the pick at which they part (if they do) and the oracle's conditioning."""
+    from .kmean_ref import kmean_select
+    from .ref_import import load_reference
+    from .synth import SynthBase
+    ref = load_reference()
+    out = {}
+    emb20 = np.load(tmp("fwd20k_emb.npy"))
+    L = N_LABELED3
+    names20 = [case_name(i) for i in range(L + N_POOL_SMALL)]
+
+    class _RefBase(SynthBase, ref.BaseDataset):
+        pass
+    base = _RefBase(torch.zeros((len(names20), 1, 1), dtype=torch.uint8), names20)
+    for metric in ("cosine", "l2"):
+        ad = ref.ActiveDataset(ref.ExtendableDataset(base, names20[:L]), ref.ExtendableDataset(base, names20[L:]))
+        sel = ref.KMeanSelector(batch_size=64, num_workers=0, pin_memory=False, metric=metric)
+        np.random.seed(KM_SEED)
+        t0 = time.time()
+        served = _CachedFeatureModel(np.concatenate([emb20[L:], emb20[:L]], 0))   # pool rows are asked for first
+        names = sel.select_next_batch(ad, BUDGET3, served, torch.device("cpu"))
+        log(f"verbatim KMeanSelector {metric} at N={len(names20)}: {time.time() - t0:.0f}s, {len(names)} names")
+        want = sorted(map(str, names))
+        # the same call with the picks in order (the selector returns an unordered set, kmean_selector.py:194)
+        from sklearn.cluster import kmeans_plusplus
+        from .kmean_ref import sample_weights, standardize_rows
+        pool_std, lab_std = standardize_rows(emb20[L:]), standardize_rows(emb20[:L])
+        w = sample_weights(pool_std, lab_std, metric, "min", 1.0, False)
+        _c, ref_idx = kmeans_plusplus(pool_std, BUDGET3, sample_weight=w, random_state=np.random.RandomState(KM_SEED))
+        # (not asserted equal to the verbatim names: the selector's weights come from sklearn's fp32 sgemm cosine /
+        # fp64 l2 and differ from the restatement's in the last ulp on some of the 20 000 rows - enough, at this size,
+        # to move a uniform draw across a cumulative-weight boundary; see the comment below)
+        idx, gap = kmean_select(emb20[L:], emb20[:L], BUDGET3, metric, "min", 1.0, False,
+                                np.random.RandomState(KM_SEED), return_gap=True)
+        # sklearn carries the winning potential as an fp32 BLAS dot (machine-specific summation order); the oracle and
+        # the GPU kernel sum it in fp64 and round.  One ulp of difference moves the next step's uniform draws by 6e-8
+        # relative, and with 20 000 cumulative-weight boundaries and 4 000 draws a run has a draw that close to a
+        # boundary about once: from there on the two runs sample different candidates.
+        div = next((i for i, (a, b) in enumerate(zip(idx, ref_idx)) if int(a) != int(b)), -1)
+        out[f"km_20k/{metric}/selected"] = np.array(want)
+        out[f"km_20k/{metric}/reference_picks"] = np.array([int(i) for i in ref_idx], np.int64)  # pool positions
+        out[f"km_20k/{metric}/oracle_picks"] = np.array([int(i) for i in idx], np.int64)
+        out[f"km_20k/{metric}/first_divergence"] = np.int64(div)
+        out[f"km_20k/{metric}/gap"] = np.float64(gap)
+
+        def potential(pos):   # the k-means++ objective of a selected set: sum_i w_i min_c |x_i - c|^2
+            x64, c64 = pool_std.astype(np.float64), pool_std[np.asarray(pos)].astype(np.float64)
+            d2 = np.full(len(x64), np.inf)
+            for a in range(0, len(c64), 50):
+                cc = c64[a:a + 50]
+                d2 = np.minimum(d2, ((x64 * x64).sum(1)[:, None] + (cc * cc).sum(1)[None] - 2 * x64 @ cc.T).min(1))
+            return float((np.maximum(d2, 0) * w.astype(np.float64)).sum())
+        verb_pos = [int(n) - L for n in want]     # case names are zero-padded global indices
+        rs2 = np.random.RandomState(KM_SEED + 1)
+        _c, other = kmeans_plusplus(pool_std, BUDGET3, sample_weight=w, random_state=rs2)   # another seed: the spread
+        pots = {"verbatim": potential(verb_pos), "oracle": potential(idx), "sklearn_on_oracle_features": potential(ref_idx),
+                "other_seed": potential(other)}
+        for k_, v_ in pots.items():
+            out[f"km_20k/{metric}/potential/{k_}"] = np.float64(v_)
+        log(f"kmean {metric}: verbatim-vs-oracle overlap {len(set(verb_pos) & set(map(int, idx)))}/{BUDGET3}; potentials {pots}")
+        log(f"kmean {metric}: oracle vs verbatim reference: first divergence at pick {div} (-1 = none), overlap "
+            f"{len(set(map(int, idx)) & set(map(int, ref_idx)))}/{BUDGET3}, conditioning gap {gap:.3e}")
+    out["km_20k/np_seed"] = np.int64(KM_SEED)
+    np.savez(tmp("kmean.npz"), **out)
+
+
 def merge():
     path = os.path.join(OUT, "configs.npz")
     out = dict(np.load(path)) if os.path.exists(path) else {}   # stages frozen by earlier runs stay
     out["versions"] = np.array(repr(versions()))
-    for f in ("c1.npz", "c2.npz", "select.npz"):
+    for f in ("c1.npz", "c2.npz", "select.npz", "kmean.npz"):
         if os.path.exists(tmp(f)):
             out.update(np.load(tmp(f)))
     np.savez_compressed(path, **out)
     log("wrote", path, os.path.getsize(path), "bytes:", sorted(out))
 
 
-STAGES = {"c1": stage_c1, "c2": stage_c2, "fwd20k": stage_fwd20k, "emb100k": stage_emb100k, "select": stage_select}
+STAGES = {"c1": stage_c1, "c2": stage_c2, "fwd20k": stage_fwd20k, "emb100k": stage_emb100k, "select": stage_select,
+          "kmean": stage_kmean}
 
 
 def main(argv):
