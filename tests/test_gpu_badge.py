@@ -88,3 +88,50 @@ def test_badge_selector_contract(golden):
     assert got == [ad0.get_pool_dataset().image_idx[i] for i in idx[:4]]
     with pytest.raises(ValueError):  # sklearn's n_samples < n_clusters
         b200al.B200BADGESelector().select_next_batch(make_active(synth_pool_u8(6), 2), 5, model, torch.device(DEV))
+
+
+def test_badge_1000_image_pool_matches_reference(golden):
+    """Forty times the pool of the cases above (tests/golden/badge_1k.npz, oracle/make_golden_badge_1k.py): every one of
+    the 1 000 reference gradient embeddings within the pseudo-label-flip bound, and the drop-in's 32 picks equal to
+    the reference BADGESelector's, in order."""
+    import b200al
+    from oracle.synth import make_active, synth_pool_u8
+    from oracle.unet_ref import OracleUNet, golden_state_dict
+    path = os.path.join(os.path.dirname(__file__), "golden", "badge_1k.npz")
+    if not os.path.exists(path):
+        pytest.skip("tests/golden/badge_1k.npz not generated (oracle/make_golden_badge_1k.py, container only)")
+    gb = np.load(path)
+    n_lab, n_pool = int(gb["n_labeled"]), int(gb["n_pool"])
+    want = gb["emb"]
+    images = synth_pool_u8(n_lab + n_pool)
+    eng = b200al.Engine(DEV, 3, max_samples=128)
+    try:
+        eng.load_model(golden_state_dict(3, golden["model"]))
+        got = eng.badge_embed(images[n_lab:].to(DEV))[:, :96].cpu().numpy()
+    finally:
+        eng.close()
+    scale = np.abs(want).max(axis=1, keepdims=True)
+    err = np.abs(got - want) / scale
+    print(f"badge 1k: max relative embedding error {err.max():.2e}, mean {err.mean():.2e}, golden k-means++ gap {float(gb['gap']):.2e}")
+    assert err.max() < 3e-3 and err.mean() < 2e-4, (err.max(), err.mean())
+    sel = b200al.B200BADGESelector(batch_size=1, num_workers=0, pin_memory=False)
+    np.random.seed(int(gb["seed"]))
+    ad = make_active(images, n_lab)
+    ref_names = gb["selected"].tolist()
+    picked = sel.select_next_batch(ad, len(ref_names), OracleUNet(golden_state_dict(3, golden["model"])), torch.device(DEV))
+    assert len(picked) == len(set(picked)) == len(ref_names) and set(picked) <= set(ad.get_pool_dataset().image_idx)
+    if picked == ref_names:
+        return
+    # 160 inverse-CDF draws over 1 000 cumulative weights: the frozen run tolerates input changes up to `gap` only
+    gap = float(gb["gap"])
+    assert gap < 10 * err.max(), f"picks differ although the run's conditioning {gap:.1e} is 10x the embedding error"
+    pos = {n: i for i, n in enumerate(ad.get_pool_dataset().image_idx)}
+    X = want.astype(np.float64)
+
+    def objective(names):   # unweighted k-means++ potential of a selected set, on the reference embeddings
+        c = X[[pos[n] for n in names]]
+        return float((((X[:, None, :] - c[None]) ** 2).sum(-1).min(1)).sum())
+    a, b = objective(picked), objective(ref_names)
+    print(f"badge 1k: picks differ from step {next(i for i, (p, q) in enumerate(zip(picked, ref_names)) if p != q)}; "
+          f"objective {a:.4e} vs the reference set's {b:.4e} ({a / b - 1:+.2%})")
+    assert abs(a / b - 1) < 0.05
