@@ -73,6 +73,7 @@ struct Layer {
   // mixed-precision scoring path (conv_tc.cuh FMT): nsplit 0 = the context's; fmt 1 = fp16 single-plane output,
   // 2 = fp16 single-plane operands and output, 3 = fp16 operands, bf16 hi/lo output
   int nsplit = 0, fmt = 0;
+  bool halo = false;       // fp16 stride-1 3x3: row-halo stages (conv_tc.cuh, template HALO)
   __half* wp16 = nullptr;  // packed single-plane fp16 weights [tap][N][Cin] (fmt >= 2)
 };
 
@@ -306,19 +307,21 @@ ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw, bool pair = false, 
 // pair: each CTA of the pair holds half of the weight tile's rows
 // planes: operand planes per pipeline stage - 2 for the bf16 hi/lo pair and for the fp16 layers (two consecutive
 // k-chunks per stage, conv_tc.cuh kKChunks), else 1
-int stage_bytes(int bn, int bk, int planes, bool pair = false, int mt = 1) {
+int stage_bytes(int bn, int bk, int planes, bool pair = false, int mt = 1, bool halo = false) {
+  if (halo) return 160 * bk * 2 + 3 * (pair ? bn / 2 : bn) * bk * 2;  // one 10-row box + three filter rows of weights
   return planes * (mt * 128 * bk * 2 + (pair ? bn / 2 : bn) * bk * 2);
 }
 int out_buf_bytes(int cw, int oplanes) { return oplanes * 128 * cw * 2; }
 int conv_smem_bytes(int bn, int bk, int planes, int oplanes, int stages, int cw, int nbufs_total, bool pair = false,
-                    int mt = 1) {
-  return stages * stage_bytes(bn, bk, planes, pair, mt) + nbufs_total * out_buf_bytes(cw, oplanes) + 1024 + 8 * bn * 4;
+                    int mt = 1, bool halo = false) {
+  return stages * stage_bytes(bn, bk, planes, pair, mt, halo) + nbufs_total * out_buf_bytes(cw, oplanes) + 1024 +
+         8 * bn * 4;
 }
 // per-layer operand split and number of output planes (conv_tc.cuh FMT)
 int layer_nsplit(const b200al_ctx* ctx, const Layer& L);
 int layer_oplanes(const b200al_ctx* ctx, const Layer& L);
 int layer_planes(const b200al_ctx* ctx, const Layer& L);
-ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt);
+ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt, bool halo = false);
 ConvKernelFn layer_kernel(const b200al_ctx* ctx, const Layer& L);
 int layer_smem(const b200al_ctx* ctx, const Layer& L);
 
@@ -435,9 +438,27 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
       L.stages = st2 > 8 ? 8 : st2;
     }
   }
+  // Row-halo stages (template HALO) for the fp16 stride-1 3x3 layers: with single operands the shared-memory refill
+  // sets the pace; one 10-row activation box per filter column serves the three filter rows, so
+  // a stage is 20 KB of activations + 3 weight tiles for 12 MMAs instead of 2 x 16 KB + 2 weight tiles for 8.
+  L.halo = false;
+  if (L.fmt == 2 && L.kind == KIND_CONV3 && L.stride == 1 && L.mt == 1 && L.bk == 64 && env_int("B200AL_HALO", 1)) {
+    int nb = L.nbuf;
+    const int sbh = stage_bytes(L.bn, 64, 1, L.pair, 1, true);
+    int sth = (kMaxSmem - fixed - L.ngroups * nb * out_buf_bytes(32, opl)) / sbh;
+    if (sth < 3 && L.ngroups == 1 && nb == 2) {
+      nb = 1;
+      sth = (kMaxSmem - fixed - L.ngroups * nb * out_buf_bytes(32, opl)) / sbh;
+    }
+    if (sth >= 3 && pick_kernel_fmt(L.bn, 64, 32, L.pair, 1, 2, true)) {
+      L.halo = true; L.cw = 32; L.nbuf = nb;
+      L.stages = sth > 8 ? 8 : sth;
+    }
+  }
   p.taps = L.kind == KIND_CONV3 ? 9 : 1;
-  p.chunks = L.cin / (L.bk * (L.fmt >= 2 ? 2 : 1));  // fp16 layers: two BK-channel chunks per pipeline stage
-  if (L.fmt >= 2 && L.cin % (2 * L.bk))
+  // fp16 layers: two BK-channel chunks per pipeline stage (row-halo stages: one chunk, three filter rows)
+  p.chunks = L.cin / (L.bk * ((L.fmt >= 2 && !L.halo) ? 2 : 1));
+  if (L.fmt >= 2 && !L.halo && L.cin % (2 * L.bk))
     return set_err(ctx, B200AL_ERR_UNSUPPORTED, "fp16 layer needs Cin %% %d == 0", 2 * L.bk);
   p.n_total = n_total;
   p.a_lo_off = ib.c_total;
@@ -517,7 +538,7 @@ int make_layer_maps(b200al_ctx* ctx, const Layer& L, const __nv_bfloat16* in, co
     return make_tma_act(ctx, tmO, out, S, outH, outW, 2 * ob.c_total, 1, 32, kFoldValid, 1);
   }
   if ((rc = make_tma_act(ctx, tmA, in, S, inH, inW, 2 * ib.c_total, L.kind == KIND_CONV3 ? L.stride : 1, L.bk, L.p.tw,
-                         L.p.th, L.cin)))
+                         L.halo ? L.p.th + 2 : L.p.th, L.cin)))
     return rc;
   // output map: box = one epilogue warp's 2 image rows x 16 px x CW channels; transposed conv uses the stride-2 view
   return make_tma_act(ctx, tmO, out, S, outH, outW, 2 * ob.c_total, L.kind == KIND_CONVT ? 2 : 1, L.cw, 16, 2);
@@ -602,7 +623,13 @@ int layer_oplanes(const b200al_ctx* ctx, const Layer& L) {
 }
 int layer_planes(const b200al_ctx* ctx, const Layer& L) { return (layer_nsplit(ctx, L) == 3 || L.fmt >= 2) ? 2 : 1; }
 // The format variants are instantiated for the tile shapes the planner gives the layers of the fp16 groups only.
-ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt) {
+ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt, bool halo) {
+  if (halo) {  // fp16 operands and output, row-halo stages (stride-1 3x3)
+    if (fmt != 2 || mt != 1 || bk != 64 || cw != 32) return nullptr;
+    if (pair && bn == 256) return (ConvKernelFn)conv_tc_kernel<256, 64, 1, 32, true, 1, 2, true>;
+    if (!pair && bn == 128) return (ConvKernelFn)conv_tc_kernel<128, 64, 1, 32, false, 1, 2, true>;
+    return nullptr;
+  }
   if (fmt == 1) {  // bf16x3 operands, fp16 output: the layer in front of a group
     if (!pair && mt == 2 && bn == 128 && bk == 32 && cw == 32) return (ConvKernelFn)conv_tc_kernel<128, 32, 3, 32, false, 2, 1>;
     if (pair && bn == 256 && bk == 64 && cw == 32) return (ConvKernelFn)conv_tc_kernel<256, 64, 3, 32, true, 1, 1>;
@@ -622,12 +649,12 @@ ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt)
   return nullptr;
 }
 ConvKernelFn layer_kernel(const b200al_ctx* ctx, const Layer& L) {
-  if (L.fmt) return pick_kernel_fmt(L.bn, L.bk, L.cw, L.pair, L.mt, L.fmt);
+  if (L.fmt) return pick_kernel_fmt(L.bn, L.bk, L.cw, L.pair, L.mt, L.fmt, L.halo);
   return pick_kernel(L.bn, L.bk, layer_nsplit(ctx, L), L.cw, L.pair, L.mt);
 }
 int layer_smem(const b200al_ctx* ctx, const Layer& L) {
   return conv_smem_bytes(L.bn, L.bk, layer_planes(ctx, L), layer_oplanes(ctx, L), L.stages, L.cw, L.nbuf * L.ngroups,
-                         L.pair, L.mt);
+                         L.pair, L.mt, L.halo);
 }
 }  // namespace
 
@@ -714,9 +741,9 @@ int finish_generic_layer(b200al_ctx* ctx, Layer& L) {
   if (L.ctas_per_sm > 2) L.ctas_per_sm = 2;
   if (L.pair || L.mt == 2) L.ctas_per_sm = 1;
   if (env_int("B200AL_VERBOSE", 0))
-    fprintf(stderr, "b200al plan: layer %d kind=%d %d->%d s%d fmt=%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d pair=%d mt=%d\n",
+    fprintf(stderr, "b200al plan: layer %d kind=%d %d->%d s%d fmt=%d BN=%d BK=%d stages=%d CW=%d nbuf=%d groups=%d smem=%d ctas/sm=%d pair=%d mt=%d halo=%d\n",
             L.index, L.kind, L.cin, L.cout, L.stride, L.fmt, L.bn, L.bk, L.stages, L.cw, L.nbuf, L.ngroups, smem_l,
-            L.ctas_per_sm, (int)L.pair, L.mt);
+            L.ctas_per_sm, (int)L.pair, L.mt, (int)L.halo);
   return 0;
 }
 

@@ -67,17 +67,23 @@ constexpr int kConvThreads = 320;  // TMA warp + MMA warp + 2 epilogue groups of
 // 3 = single fp16 operands, output a bf16 hi/lo pair again (last layer of an fp16 group).
 // A single plane always sits where the hi plane of the pair would (the lo half of the pixel stays unused).
 // smem: [stages x (A planes, B planes)] [nbuf x planes x 128 x CW staging for the TMA store] [barriers] [affine]
-template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR = false, int MT = 1, int FMT = 0>
+// HALO (fp16 stride-1 3x3 layers): a pipeline stage holds ONE activation box of 10 image rows x 16 pixels x BK
+// channels for a filter column s, and the weight tiles of the three filter rows r: tap (r, s) reads the box from image
+// row r on (whole 1024-byte swizzle groups further down, only the descriptor start address moves).  A bytes per MMA
+// drop from 9 boxes of 8 rows to 3 boxes of 10, a stage carries 3 x BK/16 MMAs per barrier hand-shake.
+template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR = false, int MT = 1, int FMT = 0, bool HALO = false>
 struct ConvTcSmem {
   // operand planes per pipeline stage: the hi/lo pair (NSPLIT == 3), or - fp16 layers (FMT >= 2) - TWO consecutive
   // BK-channel chunks, so that one barrier hand-shake feeds 2 x BK/16 MMAs instead of BK/16 (with a single MMA per
   // k-step the hand-shake latency, not the pipe, bounded these layers: profiles/r02_ncu_full_conv.csv)
-  static constexpr int kKChunks = FMT >= 2 ? 2 : 1;
+  static constexpr int kKChunks = (FMT >= 2 && !HALO) ? 2 : 1;
   static constexpr int kPlanes = (NSPLIT == 3) ? 2 : kKChunks;
   static constexpr int kOutPlanes = FMT == 0 ? ((NSPLIT == 3) ? 2 : 1) : (FMT == 3 ? 2 : 1);
-  static constexpr int kABytes = 128 * BK * 2;
+  static constexpr int kABytes = (HALO ? 160 : 128) * BK * 2;
   static constexpr int kBBytes = (PAIR ? BLOCK_N / 2 : BLOCK_N) * BK * 2;  // rows of B held by this CTA
-  static constexpr int kStageBytes = kPlanes * (MT * kABytes + kBBytes);  // [A tile(s): hi, lo per tile][B: hi, lo]
+  static constexpr int kBTaps = HALO ? 3 : 1;                              // weight tiles per stage
+  // [A tile(s): hi, lo per tile][B: hi, lo]   (HALO: [A box][B row 0][B row 1][B row 2])
+  static constexpr int kStageBytes = kPlanes * (MT * kABytes + kBTaps * kBBytes);
   static constexpr int kOutWarpBytes = 32 * CW * 2;                  // one warp's 32 rows of one plane
   static constexpr int kOutBufBytes = kOutPlanes * 4 * kOutWarpBytes;   // one staging buffer
   static constexpr int kTailBytes = 1024;  // barriers, tmem ptr
@@ -117,11 +123,12 @@ __device__ __forceinline__ bool get_tile(const ConvTcParams& p, int i, int block
   return true;
 }
 
-template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR, int MT = 1, int FMT = 0>
+template <int BLOCK_N, int BK, int NSPLIT, int CW, bool PAIR, int MT = 1, int FMT = 0, bool HALO = false>
 __global__ void __launch_bounds__(kConvThreads)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const ConvTcParams p, const int stages, const int nbuf, const int ngroups) {
-  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW, PAIR, MT, FMT>;
+  using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW, PAIR, MT, FMT, HALO>;
+  static_assert(!HALO || (FMT >= 2 && MT == 1 && BK == 64), "row-halo stages: fp16 operands, 128-byte rows");
   static_assert(BLOCK_N % CW == 0 && (CW == 32 || CW == 64), "bad store chunk width");
   static_assert(FMT == 0 || (FMT == 1 && NSPLIT == 3) || ((FMT == 2 || FMT == 3) && NSPLIT == 1), "bad operand format");
   constexpr bool A16 = FMT >= 2;              // fp16 operands
@@ -153,7 +160,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_kb = p.taps * p.chunks;
+  const int num_kb = HALO ? 3 * p.chunks : p.taps * p.chunks;  // HALO: (filter column, channel chunk)
 
   if (warp == 0 && lane == 0) {
     if (smem_u32(smem) & 1023u) {
@@ -195,6 +202,35 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tc); ++i) {
         if (MT == 2) get_tile(p, i, BLOCK_N, 1u, &tc1);
         for (int kb = 0; kb < num_kb; ++kb) {
+          if (HALO) {
+            const int s = kb / p.chunks, ch = kb - s * p.chunks;
+            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+            uint8_t* st = smem + (size_t)stage * L::kStageBytes;
+            const int c = p.a_c0[s] + ch * BK;
+            const int cx = tc.x0 + p.a_dx[s], cy = tc.y0 - 1;  // rows y0-1 .. y0+8 (out-of-range rows arrive as zeros)
+            if (PAIR) {
+              const uint32_t own = smem_u32(&full_bar[stage]);
+              const uint32_t fb = rank == 0 ? own : mapa_shared(own, 0);
+              if (rank == 0) mbar_arrive_expect_tx(own, 2 * L::kStageBytes);
+              else mbar_arrive_remote(fb);
+              tma_load_5d_pair(smem_u32(st), &tmA, fb, c, cx, 0, cy, tc.sample);
+              for (int r = 0; r < 3; ++r)
+                tma_load_2d_pair(smem_u32(st + L::kABytes + r * L::kBBytes), &tmB, fb, ch * BK,
+                                 (r * 3 + s) * p.n_total + tc.n0 + (int)rank * (BLOCK_N / 2));
+            } else {
+              const uint32_t fb = smem_u32(&full_bar[stage]);
+              mbar_arrive_expect_tx(fb, L::kStageBytes);
+              tma_load_5d(smem_u32(st), &tmA, fb, c, cx, 0, cy, tc.sample);
+              for (int r = 0; r < 3; ++r) {
+                uint8_t* bdst = st + L::kABytes + r * L::kBBytes;
+                const int row = (r * 3 + s) * p.n_total + tc.n0;
+                tma_load_2d(smem_u32(bdst), &tmB, fb, ch * BK, row);
+                tma_load_2d(smem_u32(bdst + L::kBBytes / 2), &tmB, fb, ch * BK, row + BLOCK_N / 2);
+              }
+            }
+            if (++stage == stages) { stage = 0; phase ^= 1; }
+            continue;
+          }
           const int tap = kb / p.chunks;
           const int ch = kb - tap * p.chunks;
           const int r = tap / 3, s = tap - r * 3;
@@ -263,7 +299,30 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t a_lo = a_hi + (L::kABytes >> 4);
           const uint32_t b_hi = a_hi + ((MT * L::kPlanes * L::kABytes) >> 4);
           const uint32_t b_lo = b_hi + (L::kBBytes >> 4);
-          if (elect_one()) {
+          if (HALO) {
+            if (elect_one()) {
+              const uint32_t b0 = a_hi + (L::kABytes >> 4);
+#pragma unroll
+              for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  // filter row r: the 128 pixels from image row r of the box on (16 pixels x 128 B = 2048 B per row)
+                  const uint64_t da = make_desc(a_hi + r * (2048 >> 4) + 2 * k, kDescHi);
+                  const uint64_t db = make_desc(b0 + r * (L::kBBytes >> 4) + 2 * k, kDescHi);
+                  const uint32_t accum = (kb > 0 || r > 0 || k > 0) ? 1u : 0u;
+                  if (PAIR) umma_bf16_pair(d_tmem, da, db, idesc, accum);
+                  else umma_bf16(d_tmem, da, db, idesc, accum);
+                }
+              }
+              if (PAIR) {
+                umma_commit_pair(smem_u32(&empty_bar[stage]));
+                if (kb == num_kb - 1) umma_commit_pair(smem_u32(&tfull_bar[acc]));
+              } else {
+                umma_commit(smem_u32(&empty_bar[stage]));
+                if (kb == num_kb - 1) umma_commit(smem_u32(&tfull_bar[acc]));
+              }
+            }
+          } else if (elect_one()) {
 #pragma unroll
             for (int k = 0; k < BK / 16; ++k) {
               const uint64_t da = make_desc(a_hi + 2 * k, kDescHi);
