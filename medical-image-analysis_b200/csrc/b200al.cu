@@ -308,7 +308,8 @@ ConvKernelFn pick_kernel(int bn, int bk, int nsplit, int cw, bool pair = false, 
 // planes: operand planes per pipeline stage - 2 for the bf16 hi/lo pair and for the fp16 layers (two consecutive
 // k-chunks per stage, conv_tc.cuh kKChunks), else 1
 int stage_bytes(int bn, int bk, int planes, bool pair = false, int mt = 1, bool halo = false) {
-  if (halo) return 160 * bk * 2 + 3 * (pair ? bn / 2 : bn) * bk * 2;  // one 10-row box + three filter rows of weights
+  // one 10-row box (per plane and pixel tile) + three filter rows of weights
+  if (halo) return planes * (mt * 160 * bk * 2 + 3 * (pair ? bn / 2 : bn) * bk * 2);
   return planes * (mt * 128 * bk * 2 + (pair ? bn / 2 : bn) * bk * 2);
 }
 int out_buf_bytes(int cw, int oplanes) { return oplanes * 128 * cw * 2; }
@@ -419,6 +420,7 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
   // Super-tiles (template MT = 2): the N <= 128 layers are bound by the L2->SM operand stream; two pixel tiles per
   // CTA share every weight tile, one CTA per SM with all of its shared memory.
   L.mt = 1;
+  L.halo = false;
   // Same-box A/B of bench.py (3 alternations): 1542 -> 1580 images/s (+2.5 %) with SM clocks 1477 -> 1458 MHz under
   // the power cap; per layer: stride-2 32->64 -20 %, 128->64 at 128^2 -8 %, 128->128 at 64^2 -9 %.
   // B200AL_MT2: bit 0 = the BN = 64 layers, bit 1 = the BN = 128 layers (BK = 32 there), 0 = off.
@@ -438,13 +440,24 @@ int plan_layer(b200al_ctx* ctx, Layer& L) {
       L.stages = st2 > 8 ? 8 : st2;
     }
   }
+  // The same for the bf16x3 N = 64 super-tile (decoder.levels.2.0: 128 -> 64 at 128^2), whose stages of 80 KB per 896
+  // MMA cycles ask the L2 -> SM path for 89 B/clk: with 64-byte rows (BK = 32) a stage is four 10-row boxes (two pixel
+  // tiles x hi, lo) + six weight tiles = 64 KB for 1344 cycles.
+  if (L.fmt == 0 && ns == 3 && L.kind == KIND_CONV3 && L.stride == 1 && L.mt == 2 && L.bn == 64 && !L.pair &&
+      L.cin % 32 == 0 && env_int("B200AL_HALO3", 1)) {
+    const int sbh = stage_bytes(64, 32, 2, false, 2, true);
+    const int sth = (kMaxSmem - fixed - 2 * out_buf_bytes(32, opl)) / sbh;
+    if (sth >= 3) {
+      L.halo = true; L.bk = 32; L.cw = 32; L.ngroups = 2; L.nbuf = 1;
+      L.stages = sth > 8 ? 8 : sth;
+    }
+  }
   // Row-halo stages (template HALO) for the fp16 stride-1 3x3 layers: with single operands the shared-memory refill
   // sets the pace; one 10-row activation box per filter column serves the three filter rows, so
   // a stage is 20 KB of activations + 3 weight tiles for 12 MMAs instead of 2 x 16 KB + 2 weight tiles for 8.
-  L.halo = false;
   if (L.fmt == 2 && L.kind == KIND_CONV3 && L.stride == 1 && L.mt == 1 && L.bk == 64 && env_int("B200AL_HALO", 1)) {
     int nb = L.nbuf;
-    const int sbh = stage_bytes(L.bn, 64, 1, L.pair, 1, true);
+    const int sbh = stage_bytes(L.bn, 64, 1, L.pair, 1, true);  // (planes = 1: a single chunk per stage)
     int sth = (kMaxSmem - fixed - L.ngroups * nb * out_buf_bytes(32, opl)) / sbh;
     if (sth < 3 && L.ngroups == 1 && nb == 2) {
       nb = 1;
@@ -621,7 +634,10 @@ int layer_oplanes(const b200al_ctx* ctx, const Layer& L) {
   if (L.fmt == 0) return layer_nsplit(ctx, L) == 3 ? 2 : 1;
   return L.fmt == 3 ? 2 : 1;
 }
-int layer_planes(const b200al_ctx* ctx, const Layer& L) { return (layer_nsplit(ctx, L) == 3 || L.fmt >= 2) ? 2 : 1; }
+int layer_planes(const b200al_ctx* ctx, const Layer& L) {
+  if (L.halo && L.fmt >= 2) return 1;  // row-halo fp16 stages hold one channel chunk
+  return (layer_nsplit(ctx, L) == 3 || L.fmt >= 2) ? 2 : 1;
+}
 // The format variants are instantiated for the tile shapes the planner gives the layers of the fp16 groups only.
 ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt, bool halo) {
   if (halo) {  // fp16 operands and output, row-halo stages (stride-1 3x3)
@@ -650,6 +666,11 @@ ConvKernelFn pick_kernel_fmt(int bn, int bk, int cw, bool pair, int mt, int fmt,
 }
 ConvKernelFn layer_kernel(const b200al_ctx* ctx, const Layer& L) {
   if (L.fmt) return pick_kernel_fmt(L.bn, L.bk, L.cw, L.pair, L.mt, L.fmt, L.halo);
+  if (L.halo) {  // bf16x3 N = 64 super-tile with row-halo stages
+    if (layer_nsplit(ctx, L) == 3 && L.bn == 64 && L.bk == 32 && L.cw == 32 && !L.pair && L.mt == 2)
+      return (ConvKernelFn)conv_tc_kernel<64, 32, 3, 32, false, 2, 0, true>;
+    return nullptr;
+  }
   return pick_kernel(L.bn, L.bk, layer_nsplit(ctx, L), L.cw, L.pair, L.mt);
 }
 int layer_smem(const b200al_ctx* ctx, const Layer& L) {

@@ -128,7 +128,9 @@ __global__ void __launch_bounds__(kConvThreads)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const __grid_constant__ CUtensorMap tmO, const ConvTcParams p, const int stages, const int nbuf, const int ngroups) {
   using L = ConvTcSmem<BLOCK_N, BK, NSPLIT, CW, PAIR, MT, FMT, HALO>;
-  static_assert(!HALO || (FMT >= 2 && MT == 1 && BK == 64), "row-halo stages: fp16 operands, 128-byte rows");
+  static_assert(!HALO || (FMT >= 2 && MT == 1 && BK == 64) ||
+                    (FMT == 0 && NSPLIT == 3 && MT == 2 && !PAIR && BLOCK_N == 64 && BK == 32),
+                "row-halo stages: fp16 layers (128-byte rows), or the bf16x3 N = 64 super-tile (64-byte rows)");
   static_assert(BLOCK_N % CW == 0 && (CW == 32 || CW == 64), "bad store chunk width");
   static_assert(FMT == 0 || (FMT == 1 && NSPLIT == 3) || ((FMT == 2 || FMT == 3) && NSPLIT == 1), "bad operand format");
   constexpr bool A16 = FMT >= 2;              // fp16 operands
@@ -202,6 +204,28 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int i = 0; get_tile(p, i, BLOCK_N, rank, &tc); ++i) {
         if (MT == 2) get_tile(p, i, BLOCK_N, 1u, &tc1);
         for (int kb = 0; kb < num_kb; ++kb) {
+          if (HALO && NSPLIT == 3) {
+            // bf16x3 super-tile: [tile 0: hi box, lo box][tile 1: hi, lo][filter row 0: w_hi, w_lo][row 1][row 2]
+            const int s = kb / p.chunks, ch = kb - s * p.chunks;
+            mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
+            uint8_t* st = smem + (size_t)stage * L::kStageBytes;
+            const int c = p.a_c0[s] + ch * BK, c1 = c + p.a_lo_off;
+            const uint32_t fb = smem_u32(&full_bar[stage]);
+            mbar_arrive_expect_tx(fb, L::kStageBytes);
+            tma_load_5d(smem_u32(st), &tmA, fb, c, tc.x0 + p.a_dx[s], 0, tc.y0 - 1, tc.sample);
+            tma_load_5d(smem_u32(st + L::kABytes), &tmA, fb, c1, tc.x0 + p.a_dx[s], 0, tc.y0 - 1, tc.sample);
+            tma_load_5d(smem_u32(st + 2 * L::kABytes), &tmA, fb, c, tc1.x0 + p.a_dx[s], 0, tc1.y0 - 1, tc1.sample);
+            tma_load_5d(smem_u32(st + 3 * L::kABytes), &tmA, fb, c1, tc1.x0 + p.a_dx[s], 0, tc1.y0 - 1, tc1.sample);
+            for (int r = 0; r < 3; ++r)
+              for (int pl = 0; pl < 2; ++pl) {
+                uint8_t* bdst = st + 4 * L::kABytes + (r * 2 + pl) * L::kBBytes;
+                const int row = (pl * p.taps + r * 3 + s) * p.n_total + tc.n0;
+                tma_load_2d(smem_u32(bdst), &tmB, fb, ch * BK, row);
+                tma_load_2d(smem_u32(bdst + L::kBBytes / 2), &tmB, fb, ch * BK, row + BLOCK_N / 2);
+              }
+            if (++stage == stages) { stage = 0; phase ^= 1; }
+            continue;
+          }
           if (HALO) {
             const int s = kb / p.chunks, ch = kb - s * p.chunks;
             mbar_wait(smem_u32(&empty_bar[stage]), phase ^ 1);
@@ -299,7 +323,29 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           const uint32_t a_lo = a_hi + (L::kABytes >> 4);
           const uint32_t b_hi = a_hi + ((MT * L::kPlanes * L::kABytes) >> 4);
           const uint32_t b_lo = b_hi + (L::kBBytes >> 4);
-          if (HALO) {
+          if (HALO && NSPLIT == 3) {
+            if (elect_one()) {
+              constexpr uint32_t idesc2 = umma_idesc_bf16(128, 2 * BLOCK_N);
+              constexpr uint32_t kA = L::kABytes >> 4;
+              constexpr uint32_t kRow = (16 * kRowBytes) >> 4;   // one image row of the box (16 pixels)
+              const uint32_t b0 = a_hi + 4 * kA;
+#pragma unroll
+              for (int r = 0; r < 3; ++r) {
+#pragma unroll
+                for (int k = 0; k < BK / 16; ++k) {
+                  const uint32_t ao = r * kRow + 2 * k;
+                  const uint64_t db = make_desc(b0 + r * ((2 * L::kBBytes) >> 4) + 2 * k, kDescHi);  // [w_hi ; w_lo]
+                  const uint32_t accum = (kb > 0 || r > 0 || k > 0) ? 1u : 0u;
+                  umma_bf16(d_tmem, make_desc(a_hi + ao, kDescHi), db, idesc2, accum);
+                  umma_bf16(d_tmem, make_desc(a_hi + kA + ao, kDescHi), db, idesc, 1u);
+                  umma_bf16(d_tmem + ACCW, make_desc(a_hi + 2 * kA + ao, kDescHi), db, idesc2, accum);
+                  umma_bf16(d_tmem + ACCW, make_desc(a_hi + 3 * kA + ao, kDescHi), db, idesc, 1u);
+                }
+              }
+              umma_commit(smem_u32(&empty_bar[stage]));
+              if (kb == num_kb - 1) umma_commit(smem_u32(&tfull_bar[acc]));
+            }
+          } else if (HALO) {
             if (elect_one()) {
               const uint32_t b0 = a_hi + (L::kABytes >> 4);
 #pragma unroll
